@@ -1,0 +1,203 @@
+/*
+ * bcp.h — C ABI of the B200-native batched BulletCartpole reset/step path.
+ *
+ * The reference (rebcabin/cartpoleplusplus) has no FFI layer of its own: its hot
+ * path is `bullet_cartpole.py` calling the third-party `pybullet` C extension
+ * in-process.  This header is the boundary a maintainer would bind instead of
+ * those pybullet calls; every entry point names the reference interface it
+ * replaces (file:line into the reference tree).
+ *
+ * Conventions
+ *   - extern "C", POD only, no torch types.  All tensor arguments are raw DEVICE
+ *     pointers owned by the caller (PyTorch allocates them); nothing is retained
+ *     past the call.  `stream` is a cudaStream_t passed as void*.
+ *   - every function returns 0 on success, <0 on error; the message is available
+ *     through bcp_last_error().  Nothing throws across the ABI.
+ *   - work is enqueued asynchronously on `stream`; no host synchronisation inside
+ *     reset/step/rollout.
+ */
+#ifndef BCP_H
+#define BCP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BCP_ABI_VERSION 3
+
+/* ---- dtype of the physics arithmetic ------------------------------------ */
+#define BCP_DTYPE_F32 0 /* fast mode                                          */
+#define BCP_DTYPE_F64 1 /* parity mode (pybullet's btScalar is double)        */
+
+/* ---- done reasons (info['done_reason'], bullet_cartpole.py:246,251,256) -- */
+#define BCP_REASON_NONE 0
+#define BCP_REASON_POSITION 1    /* 'out of position bounds'    :245-248 */
+#define BCP_REASON_ORIENTATION 2 /* 'out of orientation bounds' :249-253 */
+#define BCP_REASON_LENGTH 3      /* 'episode length'            :255-257 */
+
+/* ---- applyExternalForce frame (bullet_cartpole.py:203 vs the remnant :352) */
+#define BCP_FRAME_LINK 0
+#define BCP_FRAME_WORLD 1
+
+/* ---- initial-push direction draw (bullet_cartpole.py:329-332,354-359) ---- */
+#define BCP_THETA_PER_SUBSTEP 0 /* this fork: a new theta on every push substep */
+#define BCP_THETA_PER_RESET 1   /* upstream: one theta per reset                */
+
+/* One box body as the host URDF parser extracts it (models/{ground,cart,pole}.urdf). */
+typedef struct bcp_body {
+  double mass;            /* 0 => static (ground.urdf:6)                          */
+  double inertia[3];      /* effective local inertia diagonal, inertia_scaling
+                             already applied                                       */
+  double half_extents[3]; /* collision box half sizes                              */
+  double friction;        /* <lateral_friction>; Bullet default 0.5 when absent    */
+  double restitution;     /* <restitution>; Bullet default 0                       */
+  double init_pos[3];     /* loadURDF / reset position, bullet_cartpole.py:154-156 */
+} bcp_body;
+
+typedef struct bcp_config {
+  int32_t abi_version; /* must be BCP_ABI_VERSION */
+  int32_t num_envs;    /* envs owned by this handle (this rank's shard) */
+  int64_t env_id_offset; /* global id of local env 0 (RNG key => shard-invariant) */
+  uint64_t seed;
+  int32_t dtype;          /* BCP_DTYPE_* */
+  int32_t device_ordinal; /* CUDA device */
+
+  /* --- env options: add_opts, bullet_cartpole.py:15-40; ctor :50-122 --- */
+  int32_t discrete_actions;    /* ctor arg :50,:88 */
+  int32_t action_repeats;      /* --action-repeats :23 */
+  int32_t steps_per_repeat;    /* --steps-per-repeat :25 */
+  int32_t max_episode_len;     /* --max-episode-len :31 */
+  int32_t initial_force_steps; /* 30, :76 */
+  int32_t settle_steps;        /* 100, :326 */
+  int32_t random_theta;        /* !--no-random-theta :81 */
+  int32_t theta_mode;          /* BCP_THETA_* */
+  int32_t force_frame;         /* BCP_FRAME_* */
+  int32_t termination_enabled; /* the rule of :243-253 (commented out in the fork) */
+  int32_t carry_over_reset;    /* 1: reset keeps the pending force and the contact
+                                  caches exactly as pybullet does (:319-327)      */
+  int32_t reserved0;
+  double action_force;    /* --action-force :18 */
+  double initial_force;   /* --initial-force :20 */
+  double pos_threshold;   /* 3.0, :58 */
+  double angle_threshold; /* 0.35, :62 */
+  double sin_angle_threshold; /* host-precomputed sin/tan of the above: the done */
+  double tan_angle_threshold; /* test is evaluated trig-free     */
+
+  /* --- the three boxes --- */
+  bcp_body ground, cart, pole;
+
+  /* --- physics engine parameters (pybullet defaults; [BULLET-RECALL]) --- */
+  double dt;         /* 1/240 */
+  double gravity[3]; /* (0,0,-9.81) bullet_cartpole.py:152 */
+  int32_t solver_iterations; /* 50 */
+  int32_t friction_dirs;     /* 2 (btMultiBodyDynamicsWorld) */
+  int32_t cone_friction;     /* 1: implicit cone over the two directions */
+  int32_t manifold_order;    /* 0: rows in reverse pair-creation order
+                                   (ground-pole, cart-pole, ground-cart);
+                                1: creation order */
+  double residual_threshold; /* leastSquaresResidualThreshold 1e-7 */
+  double erp2;               /* 0.08 */
+  double linear_slop;        /* 1e-5 */
+  double global_cfm;         /* 0 */
+  double friction_erp;       /* 0.2 (unused: no friction anchors) */
+  double friction_cfm;       /* 0 */
+  double restitution_velocity_threshold; /* 0.2 */
+  double linear_damping;     /* 0.04f */
+  double angular_damping;    /* 0.04f */
+  double max_coordinate_velocity; /* 100 */
+  double contact_breaking_factor; /* gContactBreakingThreshold 0.02 */
+  double max_friction;       /* 10 (combined friction clamp) */
+  int32_t gyro_term;         /* 1 */
+  int32_t reserved1;
+} bcp_config;
+
+/* ---- canonical per-env state record (doubles), used by get/set_state ------
+ * and by the parity tests to start oracle and kernel from identical states.   */
+#define BCP_S_CART 0      /* pos3, quat4 (x,y,z,w), linvel3, angvel3 */
+#define BCP_S_POLE 13
+#define BCP_S_PEND_F 26   /* pending external force on the cart (world)  */
+#define BCP_S_PEND_T 29   /* pending external torque on the cart (world) */
+#define BCP_S_MANI 32     /* 3 manifolds x 4 points x 10 scalars         */
+#define BCP_MANI_POINT 10 /* localA3, localB3, normalWorldOnB3, distance */
+#define BCP_MANI_STRIDE 40
+#define BCP_S_MANI_CNT 152 /* 3 point counts */
+#define BCP_S_STEPS 155
+#define BCP_S_DONE 156
+#define BCP_S_EPISODE 157  /* number of resets so far (RNG counter word) */
+#define BCP_STATE_DOUBLES 160
+
+/* manifold (collision pair) indices, in Bullet's pair-creation order */
+#define BCP_PAIR_GROUND_CART 0
+#define BCP_PAIR_CART_POLE 1
+#define BCP_PAIR_GROUND_POLE 2
+
+/* stats record filled by bcp_stats */
+#define BCP_STATS_HEADER 4 /* episodes, env_steps, substeps, resets */
+
+typedef struct bcp_env bcp_env; /* opaque handle: one per CUDA device / shard */
+
+/* version / sizes (lets a binding check its struct mirror) */
+int bcp_abi_version(void);
+size_t bcp_config_size(void);
+const char* bcp_last_error(void);
+
+/* Replaces BulletCartpole.__init__'s world construction:
+ * p.connect/setGravity/loadURDF x3, bullet_cartpole.py:151-156.            */
+int bcp_create(const bcp_config* cfg, bcp_env** out);
+int bcp_destroy(bcp_env* env);
+
+/* Replaces BulletCartpole.reset, bullet_cartpole.py:313-346: teleport cart and
+ * pole (:319-320), 100 settle substeps (:326-327), 30 push substeps (:329-332),
+ * observation bootstrap (:338-339).
+ *   mask    : device u8[num_envs] or NULL (NULL = reset every env)
+ *   obs_out : device f32[num_envs][R][2][7] or NULL                          */
+int bcp_reset(bcp_env* env, const uint8_t* mask, float* obs_out, void* stream);
+
+/* Replaces BulletCartpole.step, bullet_cartpole.py:178-275: R x S times
+ * [p.stepSimulation(); p.applyExternalForce(cart, action*action_force)]
+ * (:197-203), pose capture per repeat (:237), steps/done/reward (:239-260).
+ *   actions : discrete  -> device i32[num_envs] in 0..4
+ *             continuous-> device f32[num_envs][2] in [-1,1]
+ *   obs_out f32[num_envs][R][2][7], reward_out f32[num_envs],
+ *   done_out u8[num_envs], reason_out u8[num_envs] (may be NULL)
+ * An env that is already done returns its old observation, reward 0, done 1
+ * (:179-181).                                                                */
+int bcp_step(bcp_env* env, const void* actions, float* obs_out, float* reward_out,
+             uint8_t* done_out, uint8_t* reason_out, void* stream);
+
+/* Random-agent protocol of README.md:76-93 run entirely on the device: n_steps
+ * env.steps per env with actions drawn in-kernel (Philox4x32-10), finished
+ * episodes recorded in the episode-length histogram and reset in place.
+ *   action_set_mask : discrete only, bit a set => action a may be drawn
+ *                     (--actions="0,1,2,3,4" == 0x1f)
+ *   obs_out may be NULL                                                      */
+int bcp_rollout_random(bcp_env* env, int32_t n_steps, uint32_t action_set_mask,
+                       float* obs_out, void* stream);
+
+/* Episode statistics accumulated on the device since the last clear:
+ *   hist : host i64[max_episode_len+1], hist[L] = episodes that ended at length L
+ *   header: host i64[BCP_STATS_HEADER] = episodes, env_steps, substeps, resets
+ *   reward_sum: host f64[1]                                                   */
+int bcp_stats(bcp_env* env, int64_t* hist, int64_t* header, double* reward_sum,
+              void* stream);
+int bcp_stats_clear(bcp_env* env, void* stream);
+
+/* Canonical state export/import (host buffers, BCP_STATE_DOUBLES doubles per
+ * env); the FP64 parity tests start oracle and kernel from identical states.   */
+int bcp_get_state(bcp_env* env, double* host_buf, size_t n_doubles, void* stream);
+int bcp_set_state(bcp_env* env, const double* host_buf, size_t n_doubles, void* stream);
+
+/* One bare p.stepSimulation() for every env (no force application, no
+ * bookkeeping) - bullet_cartpole.py:199 alone; used by single-substep parity. */
+int bcp_substep(bcp_env* env, void* stream);
+
+/* number of kernel launches this handle has enqueued (bench's gpu_launches) */
+int64_t bcp_launch_count(const bcp_env* env);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BCP_H */
