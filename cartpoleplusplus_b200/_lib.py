@@ -1,0 +1,60 @@
+"""ctypes binding of libbcp.so (include/bcp.h).  Fails loudly: there is no fallback."""
+from __future__ import annotations
+
+import ctypes
+import os
+
+from . import config as C
+
+_LIB = None
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libbcp.so")
+
+EXPORTS = ["bcp_abi_version", "bcp_config_size", "bcp_last_error", "bcp_create", "bcp_destroy", "bcp_reset",
+           "bcp_step", "bcp_rollout_random", "bcp_stats", "bcp_stats_clear", "bcp_get_state", "bcp_set_state",
+           "bcp_substep", "bcp_launch_count"]
+
+
+class BcpError(RuntimeError):
+    pass
+
+
+def load(build_if_missing: bool = False):
+    """Load the CUDA C-ABI library; raises if it is absent or its ABI does not match."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    if not os.path.exists(LIB_PATH):
+        if not build_if_missing:
+            raise BcpError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(nvcc, sm_100a).  There is no CPU fallback for the env step.")
+        from . import build as _build
+        _build.build()
+    lib = ctypes.CDLL(LIB_PATH)
+    vp, i32, u32, u64p = ctypes.c_void_p, ctypes.c_int32, ctypes.c_uint32, ctypes.c_void_p
+    lib.bcp_abi_version.restype = ctypes.c_int
+    lib.bcp_config_size.restype = ctypes.c_size_t
+    lib.bcp_last_error.restype = ctypes.c_char_p
+    lib.bcp_create.argtypes = [ctypes.POINTER(C.BcpConfig), ctypes.POINTER(vp)]
+    lib.bcp_destroy.argtypes = [vp]
+    lib.bcp_reset.argtypes = [vp, vp, vp, vp]
+    lib.bcp_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+    lib.bcp_rollout_random.argtypes = [vp, i32, u32, vp, vp]
+    lib.bcp_stats.argtypes = [vp, u64p, u64p, vp, vp]
+    lib.bcp_stats_clear.argtypes = [vp, vp]
+    lib.bcp_get_state.argtypes = [vp, vp, ctypes.c_size_t, vp]
+    lib.bcp_set_state.argtypes = [vp, vp, ctypes.c_size_t, vp]
+    lib.bcp_substep.argtypes = [vp, vp]
+    lib.bcp_launch_count.argtypes = [vp]
+    lib.bcp_launch_count.restype = ctypes.c_int64
+    if lib.bcp_abi_version() != C.BCP_ABI_VERSION:
+        raise BcpError(f"libbcp.so ABI {lib.bcp_abi_version()} != python mirror {C.BCP_ABI_VERSION}: rebuild")
+    if lib.bcp_config_size() != ctypes.sizeof(C.BcpConfig):
+        raise BcpError("sizeof(bcp_config) differs between libbcp.so and the ctypes mirror: rebuild")
+    _LIB = lib
+    return lib
+
+
+def check(rc: int, lib=None):
+    if rc != 0:
+        lib = lib or load()
+        raise BcpError((lib.bcp_last_error() or b"unknown error").decode())

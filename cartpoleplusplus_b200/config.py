@@ -16,7 +16,7 @@ from typing import Optional
 
 from . import urdf as _urdf
 
-BCP_ABI_VERSION = 3
+BCP_ABI_VERSION = 4
 DTYPE_F32, DTYPE_F64 = 0, 1
 REASON_NAMES = {0: None, 1: "out of position bounds", 2: "out of orientation bounds", 3: "episode length"}
 FRAME_LINK, FRAME_WORLD = 0, 1
@@ -24,8 +24,8 @@ THETA_PER_SUBSTEP, THETA_PER_RESET = 0, 1
 
 # canonical state record (include/bcp.h)
 S_CART, S_POLE, S_PEND_F, S_PEND_T, S_MANI = 0, 13, 26, 29, 32
-MANI_POINT, MANI_STRIDE, S_MANI_CNT = 10, 40, 152
-S_STEPS, S_DONE, S_EPISODE, STATE_DOUBLES = 155, 156, 157, 160
+MANI_POINT, MANI_STRIDE, S_MANI_CNT = 11, 44, 164
+S_STEPS, S_DONE, S_EPISODE, STATE_DOUBLES = 167, 168, 169, 176
 STATS_HEADER = 4
 
 
@@ -92,6 +92,7 @@ class BcpConfig(ctypes.Structure):
         ("max_coordinate_velocity", ctypes.c_double),
         ("contact_breaking_factor", ctypes.c_double),
         ("max_friction", ctypes.c_double),
+        ("warmstart_factor", ctypes.c_double),
         ("gyro_term", ctypes.c_int32),
         ("reserved1", ctypes.c_int32),
     ]
@@ -119,6 +120,7 @@ class PhysicsParams:
     max_coordinate_velocity: float = 100.0
     contact_breaking_factor: float = 0.02  # gContactBreakingThreshold
     max_friction: float = 10.0  # MAX_FRICTION in btManifoldResult.cpp
+    warmstart_factor: float = 0.0  # btMultiBody contact warm starting is compiled out / opt-in
     gyro_term: int = 1
     inertia_from_file: bool = False  # loadURDF without URDF_USE_INERTIA_FROM_FILE
 
@@ -199,7 +201,8 @@ def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dt
     for name in ("solver_iterations", "friction_dirs", "cone_friction", "manifold_order", "residual_threshold",
                  "erp2", "linear_slop", "global_cfm", "friction_erp", "friction_cfm",
                  "restitution_velocity_threshold", "linear_damping", "angular_damping",
-                 "max_coordinate_velocity", "contact_breaking_factor", "max_friction", "gyro_term"):
+                 "max_coordinate_velocity", "contact_breaking_factor", "max_friction", "warmstart_factor",
+                 "gyro_term"):
         setattr(c, name, getattr(physics, name))
     if c.friction_dirs not in (1, 2):
         raise ValueError("friction_dirs must be 1 or 2")

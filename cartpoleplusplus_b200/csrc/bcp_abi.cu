@@ -1,0 +1,247 @@
+// bcp_abi.cu — the extern "C" boundary of include/bcp.h over the CUDA kernels.
+// No CPU implementation exists behind these entry points: without a CUDA device
+// bcp_create fails and nothing else can be called.
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/bcp.h"
+#include "bcp_launch.cuh"
+#include "bcp_state.cuh"
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(const char* what, cudaError_t e = cudaSuccess) {
+  g_err = what;
+  if (e != cudaSuccess) {
+    g_err += ": ";
+    g_err += cudaGetErrorString(e);
+  }
+  return -1;
+}
+#define CK(call)                                  \
+  do {                                            \
+    cudaError_t _e = (call);                      \
+    if (_e != cudaSuccess) return fail(#call, _e); \
+  } while (0)
+
+}  // namespace
+
+struct bcp_env {
+  bcp_config cfg;
+  bcp::Params<float> p32;
+  bcp::Params<double> p64;
+  void* fdata = nullptr;  // SoA float fields, [NF][N] in the handle's scalar type
+  int* idata = nullptr;   // SoA int fields, [NI][N]
+  unsigned long long* hist = nullptr;
+  unsigned long long* header = nullptr;
+  double* reward_sum = nullptr;
+  int* list = nullptr;   // compacted env indices for masked resets
+  int* count = nullptr;
+  double* staging = nullptr;  // canonical records for get/set_state
+  int64_t launches = 0;
+  bool f64() const { return cfg.dtype == BCP_DTYPE_F64; }
+  bcp::StatsPtrs stats() const { return bcp::StatsPtrs{hist, header, reward_sum}; }
+};
+
+namespace {
+
+struct DeviceGuard {
+  int prev = -1;
+  explicit DeviceGuard(int dev) {
+    cudaGetDevice(&prev);
+    if (prev != dev) cudaSetDevice(dev);
+    else prev = -1;
+  }
+  ~DeviceGuard() {
+    if (prev >= 0) cudaSetDevice(prev);
+  }
+};
+
+int validate(const bcp_config* c) {
+  if (!c) return fail("bcp_create: null config");
+  if (c->abi_version != BCP_ABI_VERSION) return fail("bcp_create: abi_version mismatch");
+  if (c->num_envs < 1) return fail("bcp_create: num_envs must be >= 1");
+  if (c->dtype != BCP_DTYPE_F32 && c->dtype != BCP_DTYPE_F64) return fail("bcp_create: bad dtype");
+  if (c->action_repeats < 1 || c->steps_per_repeat < 1 || c->max_episode_len < 1)
+    return fail("bcp_create: action_repeats, steps_per_repeat, max_episode_len must be >= 1");
+  if (c->friction_dirs != 1 && c->friction_dirs != 2) return fail("bcp_create: friction_dirs must be 1 or 2");
+  if (c->solver_iterations < 1) return fail("bcp_create: solver_iterations must be >= 1");
+  if (!(c->dt > 0)) return fail("bcp_create: dt must be > 0");
+  if (!(c->cart.mass > 0) || !(c->pole.mass > 0)) return fail("bcp_create: cart and pole need positive mass");
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bcp_abi_version(void) { return BCP_ABI_VERSION; }
+size_t bcp_config_size(void) { return sizeof(bcp_config); }
+const char* bcp_last_error(void) { return g_err.c_str(); }
+
+int bcp_create(const bcp_config* cfg, bcp_env** out) {
+  if (!out) return fail("bcp_create: null out");
+  *out = nullptr;
+  if (validate(cfg)) return -1;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0) return fail("bcp_create: no CUDA device (this library has no CPU path)", e);
+  if (cfg->device_ordinal < 0 || cfg->device_ordinal >= ndev) return fail("bcp_create: device_ordinal out of range");
+  bcp_env* h = new (std::nothrow) bcp_env();
+  if (!h) return fail("bcp_create: out of host memory");
+  h->cfg = *cfg;
+  h->p32 = bcp::make_params<float>(*cfg);
+  h->p64 = bcp::make_params<double>(*cfg);
+  DeviceGuard g(cfg->device_ordinal);
+  const size_t N = (size_t)cfg->num_envs;
+  const size_t fbytes = h->f64() ? bcp::Launch<double>::state_bytes(cfg->num_envs) : bcp::Launch<float>::state_bytes(cfg->num_envs);
+  const size_t nb = (size_t)cfg->max_episode_len + 1;
+  cudaError_t err = cudaSuccess;
+  auto A = [&](void** p, size_t bytes) {
+    if (err == cudaSuccess) err = cudaMalloc(p, bytes);
+    if (err == cudaSuccess) err = cudaMemset(*p, 0, bytes);
+  };
+  A(&h->fdata, fbytes);
+  A((void**)&h->idata, (size_t)bcp::NI * N * sizeof(int));
+  A((void**)&h->hist, nb * sizeof(unsigned long long));
+  A((void**)&h->header, BCP_STATS_HEADER * sizeof(unsigned long long));
+  A((void**)&h->reward_sum, sizeof(double));
+  A((void**)&h->list, N * sizeof(int));
+  A((void**)&h->count, sizeof(int));
+  if (err == cudaSuccess) {  // no state until reset (bullet_cartpole.py:147-148): every env starts "done"
+    std::vector<int> ones(N, 1);
+    err = cudaMemcpy(h->idata + (size_t)bcp::I_DONE * N, ones.data(), N * sizeof(int), cudaMemcpyHostToDevice);
+  }
+  if (err != cudaSuccess) {
+    bcp_destroy(h);
+    return fail("bcp_create: device allocation failed", err);
+  }
+  *out = h;
+  return 0;
+}
+
+int bcp_destroy(bcp_env* h) {
+  if (!h) return 0;
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaFree(h->fdata); cudaFree(h->idata); cudaFree(h->hist); cudaFree(h->header);
+  cudaFree(h->reward_sum); cudaFree(h->list); cudaFree(h->count); cudaFree(h->staging);
+  delete h;
+  return 0;
+}
+
+int bcp_reset(bcp_env* h, const uint8_t* mask, float* obs_out, void* stream) {
+  if (!h) return fail("bcp_reset: null handle");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int* list = nullptr;
+  if (mask) {
+    CK(bcp::launch_compact(mask, h->cfg.num_envs, h->list, h->count, s));
+    h->launches++;
+    list = h->list;
+  }
+  if (h->f64()) CK(bcp::Launch<double>::reset(h->p64, h->fdata, h->idata, list, h->count, h->cfg.num_envs, obs_out, s));
+  else CK(bcp::Launch<float>::reset(h->p32, h->fdata, h->idata, list, h->count, h->cfg.num_envs, obs_out, s));
+  h->launches++;
+  return 0;
+}
+
+int bcp_step(bcp_env* h, const void* actions, float* obs_out, float* reward_out, uint8_t* done_out,
+             uint8_t* reason_out, void* stream) {
+  if (!h) return fail("bcp_step: null handle");
+  if (!actions) return fail("bcp_step: null actions");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (h->f64()) CK(bcp::Launch<double>::step(h->p64, h->fdata, h->idata, actions, obs_out, reward_out, done_out, reason_out, h->stats(), s));
+  else CK(bcp::Launch<float>::step(h->p32, h->fdata, h->idata, actions, obs_out, reward_out, done_out, reason_out, h->stats(), s));
+  h->launches++;
+  return 0;
+}
+
+int bcp_substep(bcp_env* h, void* stream) {
+  if (!h) return fail("bcp_substep: null handle");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (h->f64()) CK(bcp::Launch<double>::substep(h->p64, h->fdata, h->idata, s));
+  else CK(bcp::Launch<float>::substep(h->p32, h->fdata, h->idata, s));
+  h->launches++;
+  return 0;
+}
+
+int bcp_rollout_random(bcp_env* h, int32_t n_steps, uint32_t action_set_mask, float* obs_out, void* stream) {
+  if (!h) return fail("bcp_rollout_random: null handle");
+  if (n_steps < 0) return fail("bcp_rollout_random: n_steps < 0");
+  if (h->cfg.discrete_actions && (action_set_mask & 0x1fu) == 0) return fail("bcp_rollout_random: empty action set");
+  if (n_steps == 0) return 0;
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (h->f64()) CK(bcp::Launch<double>::rollout(h->p64, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, obs_out, h->stats(), s));
+  else CK(bcp::Launch<float>::rollout(h->p32, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, obs_out, h->stats(), s));
+  h->launches++;
+  return 0;
+}
+
+int bcp_stats(bcp_env* h, int64_t* hist, int64_t* header, double* reward_sum, void* stream) {
+  if (!h) return fail("bcp_stats: null handle");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t nb = (size_t)h->cfg.max_episode_len + 1;
+  if (hist) CK(cudaMemcpyAsync(hist, h->hist, nb * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  if (header) CK(cudaMemcpyAsync(header, h->header, BCP_STATS_HEADER * sizeof(int64_t), cudaMemcpyDeviceToHost, s));
+  if (reward_sum) CK(cudaMemcpyAsync(reward_sum, h->reward_sum, sizeof(double), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+int bcp_stats_clear(bcp_env* h, void* stream) {
+  if (!h) return fail("bcp_stats_clear: null handle");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(cudaMemsetAsync(h->hist, 0, ((size_t)h->cfg.max_episode_len + 1) * sizeof(unsigned long long), s));
+  CK(cudaMemsetAsync(h->header, 0, BCP_STATS_HEADER * sizeof(unsigned long long), s));
+  CK(cudaMemsetAsync(h->reward_sum, 0, sizeof(double), s));
+  return 0;
+}
+
+static int ensure_staging(bcp_env* h) {
+  if (!h->staging) CK(cudaMalloc((void**)&h->staging, (size_t)h->cfg.num_envs * BCP_STATE_DOUBLES * sizeof(double)));
+  return 0;
+}
+
+int bcp_get_state(bcp_env* h, double* host_buf, size_t n_doubles, void* stream) {
+  if (!h || !host_buf) return fail("bcp_get_state: null argument");
+  const size_t need = (size_t)h->cfg.num_envs * BCP_STATE_DOUBLES;
+  if (n_doubles < need) return fail("bcp_get_state: buffer too small");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (ensure_staging(h)) return -1;
+  if (h->f64()) CK(bcp::Launch<double>::export_state(h->cfg.num_envs, h->fdata, h->idata, h->staging, s));
+  else CK(bcp::Launch<float>::export_state(h->cfg.num_envs, h->fdata, h->idata, h->staging, s));
+  h->launches++;
+  CK(cudaMemcpyAsync(host_buf, h->staging, need * sizeof(double), cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+int bcp_set_state(bcp_env* h, const double* host_buf, size_t n_doubles, void* stream) {
+  if (!h || !host_buf) return fail("bcp_set_state: null argument");
+  const size_t need = (size_t)h->cfg.num_envs * BCP_STATE_DOUBLES;
+  if (n_doubles < need) return fail("bcp_set_state: buffer too small");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (ensure_staging(h)) return -1;
+  CK(cudaMemcpyAsync(h->staging, host_buf, need * sizeof(double), cudaMemcpyHostToDevice, s));
+  if (h->f64()) CK(bcp::Launch<double>::import_state(h->cfg.num_envs, h->fdata, h->idata, h->staging, s));
+  else CK(bcp::Launch<float>::import_state(h->cfg.num_envs, h->fdata, h->idata, h->staging, s));
+  h->launches++;
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+int64_t bcp_launch_count(const bcp_env* h) { return h ? h->launches : 0; }
+
+}  // extern "C"

@@ -1,0 +1,31 @@
+// bcp_launch.cuh — host-side launch interface, one explicit instantiation per scalar
+// (bcp_f32.cu: fast mode, FMA contraction on; bcp_f64.cu: parity mode, -fmad=false).
+#pragma once
+#include <cuda_runtime.h>
+#include "bcp_types.cuh"
+
+namespace bcp {
+
+struct StatsPtrs {
+  unsigned long long* hist;
+  unsigned long long* header;
+  double* reward_sum;
+};
+
+template <typename T> struct Launch {
+  static size_t state_bytes(int n_envs);  // bytes of the float-field SoA block
+  static cudaError_t step(const Params<T>& P, void* f, int* id, const void* actions, float* obs, float* reward,
+                          uint8_t* done, uint8_t* reason, StatsPtrs stats, cudaStream_t s);
+  // list == nullptr: every env; else the first *count entries of list
+  static cudaError_t reset(const Params<T>& P, void* f, int* id, const int* list, const int* count, int max_count,
+                           float* obs, cudaStream_t s);
+  static cudaError_t substep(const Params<T>& P, void* f, int* id, cudaStream_t s);
+  static cudaError_t rollout(const Params<T>& P, void* f, int* id, int n_steps, uint32_t action_mask, float* obs,
+                             StatsPtrs stats, cudaStream_t s);
+  static cudaError_t export_state(int n, const void* f, const int* id, double* out, cudaStream_t s);
+  static cudaError_t import_state(int n, void* f, int* id, const double* in, cudaStream_t s);
+};
+
+cudaError_t launch_compact(const uint8_t* flag, int n, int* list, int* count, cudaStream_t s);
+
+}  // namespace bcp

@@ -1,0 +1,205 @@
+"""BatchedBulletCartpole — the reference's gym surface over the CUDA C-ABI.
+
+Mirrors `bullet_cartpole.BulletCartpole` (bullet_cartpole.py:48-359): same constructor
+arguments `(opts, discrete_actions)`, same `reset()` / `step(action)` / `action_space` /
+`observation_space` / no-op `configure`, `seed`, `render`; the batch dimension is new.
+Tensors are PyTorch CUDA tensors; the extension only ever sees their raw pointers.
+
+`BulletCartpole` below is the `num_envs == 1` drop-in returning NumPy values exactly like
+the reference (obs `(R,2,7)` float32 copy, python float reward, bool done, info dict).
+"""
+from __future__ import annotations
+
+import ctypes
+import sys
+from typing import Optional
+
+import numpy as np
+import torch
+
+from . import _lib, spaces
+from . import config as C
+
+
+class BatchedBulletCartpole:
+    def __init__(self, opts, discrete_actions: bool, num_envs: Optional[int] = None, device=None,
+                 dtype: Optional[str] = None, seed: Optional[int] = None, env_id_offset: int = 0,
+                 physics: Optional[C.PhysicsParams] = None, scene=None):
+        if not torch.cuda.is_available():
+            raise _lib.BcpError("BatchedBulletCartpole needs a CUDA device: the env step has no CPU path")
+        self._lib = _lib.load()
+        if device is None:
+            device = getattr(opts, "device", 0)
+        self.device = torch.device("cuda", int(device) if not isinstance(device, torch.device) else device.index or 0)
+        self.cfg = C.make_config(opts, discrete_actions, num_envs=num_envs, dtype=dtype, seed=seed,
+                                 device=self.device.index, env_id_offset=env_id_offset, physics=physics, scene=scene)
+        self.num_envs = int(self.cfg.num_envs)
+        self.discrete_actions = bool(discrete_actions)
+        self.repeats = int(self.cfg.action_repeats)
+        self.steps_per_repeat = int(self.cfg.steps_per_repeat)
+        self.max_episode_len = int(self.cfg.max_episode_len)
+        # spaces, bullet_cartpole.py:91-94,138-141
+        self.action_space = spaces.Discrete(5) if discrete_actions else spaces.Box(-1.0, 1.0, shape=(1, 2))
+        float_max = np.finfo(np.float32).max
+        self.observation_space = spaces.Box(-float_max, float_max, (self.repeats, 2, 7))
+        h = ctypes.c_void_p()
+        _lib.check(self._lib.bcp_create(ctypes.byref(self.cfg), ctypes.byref(h)), self._lib)
+        self._h = h
+        n, dev = self.num_envs, self.device
+        self.obs = torch.zeros((n, self.repeats, 2, 7), dtype=torch.float32, device=dev)
+        self.reward = torch.zeros(n, dtype=torch.float32, device=dev)
+        self.done = torch.ones(n, dtype=torch.uint8, device=dev)  # no state until reset (:147-148)
+        self.reason = torch.zeros(n, dtype=torch.uint8, device=dev)
+        self._was_reset = False
+
+    # ---- gym no-ops, bullet_cartpole.py:169-176 ----
+    def configure(self, display=None):
+        pass
+
+    def seed(self, seed=None):
+        pass
+
+    def render(self, mode=None, close=None):
+        pass
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.bcp_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ---- reset, bullet_cartpole.py:313-346 ----
+    def reset(self, mask: Optional[torch.Tensor] = None, copy: bool = True) -> torch.Tensor:
+        """Reset every env (mask None) or the envs where `mask` is non-zero.  Returns obs (B,R,2,7)."""
+        mp = None
+        if mask is not None:
+            if not self._was_reset:
+                raise _lib.BcpError("first reset() must reset every env")
+            mask = mask.to(device=self.device, dtype=torch.uint8).contiguous()
+            if mask.shape != (self.num_envs,):
+                raise ValueError(f"mask must have shape ({self.num_envs},)")
+            mp = ctypes.c_void_p(mask.data_ptr())
+        _lib.check(self._lib.bcp_reset(self._h, mp, ctypes.c_void_p(self.obs.data_ptr()), self._stream()), self._lib)
+        if mask is None:
+            self.done.zero_()
+        else:
+            self.done.masked_fill_(mask.bool(), 0)
+        self._was_reset = True
+        return self.obs.clone() if copy else self.obs
+
+    # ---- step, bullet_cartpole.py:178-275 ----
+    def _actions_tensor(self, actions) -> torch.Tensor:
+        n = self.num_envs
+        if self.discrete_actions:
+            a = torch.as_tensor(actions, device=self.device)
+            if a.dtype.is_floating_point:
+                raise TypeError("discrete actions must be integers in 0..4")
+            a = a.to(torch.int32).reshape(-1)
+            if a.numel() == 1 and n > 1:
+                a = a.expand(n)
+            if a.numel() != n:
+                raise ValueError(f"expected {n} discrete actions, got {a.numel()}")
+            return a.contiguous()
+        a = torch.as_tensor(actions, dtype=torch.float32, device=self.device)
+        if a.numel() != 2 * n:
+            raise ValueError(f"expected continuous actions of shape ({n},2) or ({n},1,2), got {tuple(a.shape)}")
+        return a.reshape(n, 2).contiguous()
+
+    def step(self, actions, copy: bool = True):
+        """-> (obs (B,R,2,7) f32, reward (B,) f32, done (B,) bool, info {'done_reason': (B,) u8 codes})."""
+        if not self._was_reset:
+            raise _lib.BcpError("step() before reset()")
+        a = self._actions_tensor(actions)
+        _lib.check(self._lib.bcp_step(self._h, ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(self.obs.data_ptr()),
+                                      ctypes.c_void_p(self.reward.data_ptr()), ctypes.c_void_p(self.done.data_ptr()),
+                                      ctypes.c_void_p(self.reason.data_ptr()), self._stream()), self._lib)
+        info = {"done_reason": self.reason.clone() if copy else self.reason}
+        if copy:
+            return self.obs.clone(), self.reward.clone(), self.done.bool(), info
+        return self.obs, self.reward, self.done.bool(), info
+
+    # ---- device-side random-agent protocol (README.md:76-93) ----
+    def rollout_random(self, n_steps: int, actions=(0, 1, 2, 3, 4)):
+        if not self._was_reset:
+            self.reset(copy=False)
+        mask = 0
+        for a in actions:
+            if not 0 <= int(a) <= 4:
+                raise ValueError("discrete actions are 0..4")
+            mask |= 1 << int(a)
+        _lib.check(self._lib.bcp_rollout_random(self._h, int(n_steps), mask, ctypes.c_void_p(self.obs.data_ptr()),
+                                                self._stream()), self._lib)
+
+    def stats(self):
+        """(hist int64[max_len+1], dict(episodes, env_steps, substeps, resets), reward_sum)."""
+        hist = np.zeros(self.max_episode_len + 1, dtype=np.int64)
+        header = np.zeros(C.STATS_HEADER, dtype=np.int64)
+        rsum = np.zeros(1, dtype=np.float64)
+        _lib.check(self._lib.bcp_stats(self._h, hist.ctypes.data_as(ctypes.c_void_p),
+                                       header.ctypes.data_as(ctypes.c_void_p),
+                                       rsum.ctypes.data_as(ctypes.c_void_p), self._stream()), self._lib)
+        names = ("episodes", "env_steps", "substeps", "resets")
+        return hist, dict(zip(names, (int(v) for v in header))), float(rsum[0])
+
+    def clear_stats(self):
+        _lib.check(self._lib.bcp_stats_clear(self._h, self._stream()), self._lib)
+
+    # ---- raw physics access used by parity tests ----
+    def substep(self):
+        _lib.check(self._lib.bcp_substep(self._h, self._stream()), self._lib)
+
+    def get_state(self) -> np.ndarray:
+        buf = np.zeros((self.num_envs, C.STATE_DOUBLES), dtype=np.float64)
+        _lib.check(self._lib.bcp_get_state(self._h, buf.ctypes.data_as(ctypes.c_void_p), buf.size, self._stream()),
+                   self._lib)
+        return buf
+
+    def set_state(self, state: np.ndarray):
+        buf = np.ascontiguousarray(state, dtype=np.float64)
+        if buf.shape != (self.num_envs, C.STATE_DOUBLES):
+            raise ValueError(f"state must have shape ({self.num_envs},{C.STATE_DOUBLES})")
+        _lib.check(self._lib.bcp_set_state(self._h, buf.ctypes.data_as(ctypes.c_void_p), buf.size, self._stream()),
+                   self._lib)
+        self.done.copy_(torch.from_numpy(buf[:, C.S_DONE].astype(np.uint8)))
+        self._was_reset = True
+
+    state_dict = get_state
+    load_state_dict = set_state
+
+    @property
+    def launch_count(self) -> int:
+        return int(self._lib.bcp_launch_count(self._h))
+
+
+class BulletCartpole(BatchedBulletCartpole):
+    """Single-env drop-in with the reference's exact return types (bullet_cartpole.py:48)."""
+
+    def __init__(self, opts, discrete_actions: bool, **kw):
+        kw["num_envs"] = 1
+        super().__init__(opts, discrete_actions, **kw)
+
+    def reset(self):
+        return super().reset(copy=False)[0].cpu().numpy().copy()
+
+    def step(self, action):
+        if bool(self.done[0].item()):  # :179-181
+            print("calling step after done????", file=sys.stderr)
+            return self.obs[0].cpu().numpy().copy(), 0, True, {}
+        if self.discrete_actions:
+            a = np.asarray(action).reshape(-1)[:1].astype(np.int64)
+        else:
+            a = np.asarray(action, dtype=np.float32).reshape(1, 2)
+        obs, _reward, done, info = super().step(a, copy=False)
+        out = {}
+        code = int(info["done_reason"][0].item())
+        if code:
+            out["done_reason"] = C.REASON_NAMES[code]
+        return obs[0].cpu().numpy().copy(), 1.0, bool(done[0].item()), out

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define BCP_ABI_VERSION 3
+#define BCP_ABI_VERSION 4
 
 /* ---- dtype of the physics arithmetic ------------------------------------ */
 #define BCP_DTYPE_F32 0 /* fast mode                                          */
@@ -110,6 +110,9 @@ typedef struct bcp_config {
   double max_coordinate_velocity; /* 100 */
   double contact_breaking_factor; /* gContactBreakingThreshold 0.02 */
   double max_friction;       /* 10 (combined friction clamp) */
+  double warmstart_factor;   /* 0: contact warm starting off, as btMultiBody
+                                ships (SOLVER_USE_ARTICULATED_WARMSTARTING unset);
+                                >0: cached normal impulse x factor           */
   int32_t gyro_term;         /* 1 */
   int32_t reserved1;
 } bcp_config;
@@ -120,14 +123,15 @@ typedef struct bcp_config {
 #define BCP_S_POLE 13
 #define BCP_S_PEND_F 26   /* pending external force on the cart (world)  */
 #define BCP_S_PEND_T 29   /* pending external torque on the cart (world) */
-#define BCP_S_MANI 32     /* 3 manifolds x 4 points x 10 scalars         */
-#define BCP_MANI_POINT 10 /* localA3, localB3, normalWorldOnB3, distance */
-#define BCP_MANI_STRIDE 40
-#define BCP_S_MANI_CNT 152 /* 3 point counts */
-#define BCP_S_STEPS 155
-#define BCP_S_DONE 156
-#define BCP_S_EPISODE 157  /* number of resets so far (RNG counter word) */
-#define BCP_STATE_DOUBLES 160
+#define BCP_S_MANI 32     /* 3 manifolds x 4 points x 11 scalars         */
+#define BCP_MANI_POINT 11 /* localA3, localB3, normalWorldOnB3, distance,
+                             applied normal impulse (warm-start cache)   */
+#define BCP_MANI_STRIDE 44
+#define BCP_S_MANI_CNT 164 /* 3 point counts */
+#define BCP_S_STEPS 167
+#define BCP_S_DONE 168
+#define BCP_S_EPISODE 169  /* number of resets so far (RNG counter word) */
+#define BCP_STATE_DOUBLES 176
 
 /* manifold (collision pair) indices, in Bullet's pair-creation order */
 #define BCP_PAIR_GROUND_CART 0

@@ -200,6 +200,7 @@ typedef struct {
 } obody;
 typedef struct {
   real la[3], lb[3], n[3], dist; /* localPointA/B, normalWorldOnB, distance1 */
+  real imp;                      /* m_appliedImpulse (warm-start cache) */
 } opoint;
 typedef struct {
   int count;
@@ -239,6 +240,7 @@ static void load_state(const double* s, ostate* st) {
       opoint* o = &st->mani[m].p[k];
       for (i = 0; i < 3; ++i) { o->la[i] = (real)p[i]; o->lb[i] = (real)p[3 + i]; o->n[i] = (real)p[6 + i]; }
       o->dist = (real)p[9];
+      o->imp = (real)p[10];
     }
   }
   st->steps = (int)s[BCP_S_STEPS];
@@ -263,6 +265,7 @@ static void store_state(const ostate* st, double* s) {
         p[6 + i] = live ? o->n[i] : 0.0;
       }
       p[9] = live ? o->dist : 0.0;
+      p[10] = live ? o->imp : 0.0;
     }
   }
   s[BCP_S_STEPS] = st->steps;
@@ -662,6 +665,7 @@ static void manifold_add(omanifold* m, const oposed* A, const oposed* B, const o
   matT_mul_vec(B->R, v, np.lb);
   for (i = 0; i < 3; ++i) np.n[i] = c->n[i];
   np.dist = c->depth;
+  np.imp = 0;
   /* getCacheEntry */
   shortest = breaking * breaking;
   for (i = 0; i < m->count; ++i) {
@@ -671,7 +675,8 @@ static void manifold_add(omanifold* m, const oposed* A, const oposed* B, const o
     if (dd < shortest) { shortest = dd; nearest = i; }
   }
   if (nearest >= 0) {
-    m->p[nearest] = np; /* replaceContactPoint */
+    np.imp = m->p[nearest].imp; /* replaceContactPoint keeps m_appliedImpulse */
+    m->p[nearest] = np;
   } else {
     insert = m->count;
     if (insert == 4) insert = sort_cached_points(m, &np);
@@ -853,7 +858,7 @@ static void setup_row(const bcp_config* cfg, orow* row, sbody* bodies, int ia, i
   if (!is_friction) { row->lower = 0; row->upper = R(1e10f); }
   else { row->lower = -row->friction; row->upper = row->friction; }
   row->cfm = cfm * row->jacDiagABInv;
-  row->applied = 0; /* contact warm starting is disabled for btMultiBody */
+  row->applied = 0; /* contact warm starting is disabled for btMultiBody; see warm_start_row */
   (void)erp;
 }
 
@@ -868,6 +873,16 @@ static real jdotdv(const sbody* b, const real jac[6]) {
   if (!b->dyn) return 0;
   for (i = 0; i < 6; ++i) s += jac[i] * b->dvel[i];
   return s;
+}
+
+/* optional contact warm starting (SOLVER_USE_ARTICULATED_WARMSTARTING path of
+ * setupMultiBodyContactConstraint): cached impulse x factor applied up front */
+static void warm_start_row(orow* c, sbody* bodies, real cached, real factor) {
+  c->applied = cached * factor;
+  if (c->applied != R(0.0)) {
+    apply_delta(&bodies[c->a], c->unitA, c->applied);
+    apply_delta(&bodies[c->b], c->unitB, c->applied);
+  }
 }
 
 /* resolveSingleConstraintRowGeneric */
@@ -1040,6 +1055,7 @@ static void substep(const bcp_config* cfg, ostate* st, osubstep_info* info) {
       const int fi = n_n;
       setup_row(cfg, &nrows[n_n], bodies, pairA[m], pairB[m], wp[m][j].pa, wp[m][j].pb, mf->p[j].n, mf->p[j].dist,
                 mu, rest, 0);
+      if (cfg->warmstart_factor > 0.0) warm_start_row(&nrows[n_n], bodies, mf->p[j].imp, (real)cfg->warmstart_factor);
       n_n++;
       if (mu != R(0.0)) {
         real d1[3], d2[3];
@@ -1100,6 +1116,15 @@ static void substep(const bcp_config* cfg, ostate* st, osubstep_info* info) {
     if (lsr <= (real)cfg->residual_threshold || it >= cfg->solver_iterations - 1) { it++; break; }
   }
   if (info) { info->iterations = it; info->rows = n_n; info->friction_rows = n_f; }
+
+  /* solveGroupCacheFriendlyFinish: applied normal impulses -> manifold cache */
+  {
+    int row = 0, j;
+    for (k = 0; k < 3; ++k) {
+      m = order[k];
+      for (j = 0; j < st->mani[m].count; ++j) st->mani[m].p[j].imp = nrows[row++].applied;
+    }
+  }
 
   /* ---- 5. write back velocities, integrate transforms ---- */
   {
