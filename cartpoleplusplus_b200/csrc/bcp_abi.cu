@@ -242,6 +242,13 @@ int bcp_set_state(bcp_env* h, const double* host_buf, size_t n_doubles, void* st
   return 0;
 }
 
+int bcp_bench_fma_peak(int device_ordinal, int use_f64, int iters, double* tflops_out) {
+  if (!tflops_out || iters < 1) return fail("bcp_bench_fma_peak: bad argument");
+  DeviceGuard g(device_ordinal);
+  CK(bcp::launch_fma_peak(use_f64, iters, tflops_out));
+  return 0;
+}
+
 int64_t bcp_launch_count(const bcp_env* h) { return h ? h->launches : 0; }
 
 }  // extern "C"

@@ -8,4 +8,48 @@ cudaError_t launch_compact(const uint8_t* flag, int n, int* list, int* count, cu
   k_compact<<<(n + 255) / 256, 256, 0, s>>>(flag, n, list, count);
   return cudaGetLastError();
 }
+
+// FMA-chain microbenchmark: 8 independent accumulators per thread, no memory traffic.
+template <typename T> __global__ void k_fma_peak(T* out, int iters, T a, T b) {
+  T x0 = a, x1 = a + T(1), x2 = a + T(2), x3 = a + T(3), x4 = a + T(4), x5 = a + T(5), x6 = a + T(6), x7 = a + T(7);
+  for (int i = 0; i < iters; ++i) {
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+      x0 = fma(x0, b, a); x1 = fma(x1, b, a); x2 = fma(x2, b, a); x3 = fma(x3, b, a);
+      x4 = fma(x4, b, a); x5 = fma(x5, b, a); x6 = fma(x6, b, a); x7 = fma(x7, b, a);
+    }
+  }
+  const T s = ((x0 + x1) + (x2 + x3)) + ((x4 + x5) + (x6 + x7));
+  if (s == T(12345.678)) out[0] = s;  // keeps the chains alive
+}
+cudaError_t launch_fma_peak(int use_f64, int iters, double* tflops) {
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  void* out = nullptr;
+  cudaError_t err = cudaMalloc(&out, 64);
+  if (err != cudaSuccess) return err;
+  const int blocks = sms * 8, threads = 256;
+  cudaEvent_t e0, e1;
+  cudaEventCreate(&e0);
+  cudaEventCreate(&e1);
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; ++rep) {
+    cudaEventRecord(e0);
+    if (use_f64) k_fma_peak<double><<<blocks, threads>>>((double*)out, iters, 0.5, 0.999);
+    else k_fma_peak<float><<<blocks, threads>>>((float*)out, iters, 0.5f, 0.999f);
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    if (rep > 0 && ms < best) best = ms;
+  }
+  err = cudaGetLastError();
+  cudaEventDestroy(e0);
+  cudaEventDestroy(e1);
+  cudaFree(out);
+  const double flops = 2.0 * 64.0 * (double)iters * (double)blocks * (double)threads;
+  *tflops = flops / (best * 1e-3) / 1e12;
+  return err;
+}
 }  // namespace bcp

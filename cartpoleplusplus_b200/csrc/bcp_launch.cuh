@@ -26,6 +26,7 @@ template <typename T> struct Launch {
   static cudaError_t import_state(int n, void* f, int* id, const double* in, cudaStream_t s);
 };
 
+cudaError_t launch_fma_peak(int use_f64, int iters, double* tflops);
 cudaError_t launch_compact(const uint8_t* flag, int n, int* list, int* count, cudaStream_t s);
 
 }  // namespace bcp

@@ -126,6 +126,36 @@ class BatchedBulletCartpole:
             return self.obs.clone(), self.reward.clone(), self.done.bool(), info
         return self.obs, self.reward, self.done.bool(), info
 
+    # ---- host-buffer call: what a CPU-side agent loop uses (pinned buffers, one sync) ----
+    def step_host(self, actions_host: torch.Tensor, auto_reset: bool = False):
+        """env.step with HOST tensors: H2D of the actions, the step kernel, (optionally) the
+        reset of finished envs, D2H of obs/reward/done into pinned buffers, one stream sync.
+        Returns pinned CPU tensors (overwritten by the next call)."""
+        if not hasattr(self, "_h_obs"):
+            self._h_obs = torch.empty(self.obs.shape, dtype=torch.float32).pin_memory()
+            self._h_reward = torch.empty(self.num_envs, dtype=torch.float32).pin_memory()
+            self._h_done = torch.empty(self.num_envs, dtype=torch.uint8).pin_memory()
+            adt = torch.int32 if self.discrete_actions else torch.float32
+            ashape = (self.num_envs,) if self.discrete_actions else (self.num_envs, 2)
+            self._d_act = torch.empty(ashape, dtype=adt, device=self.device)
+        self._d_act.copy_(actions_host.reshape(self._d_act.shape), non_blocking=True)
+        obs, reward, done, _ = self.step(self._d_act, copy=False)
+        self._h_obs.copy_(obs, non_blocking=True)
+        self._h_reward.copy_(reward, non_blocking=True)
+        self._h_done.copy_(self.done, non_blocking=True)
+        if auto_reset:  # the next observation of a finished env is its reset observation
+            self.reset(mask=self.done, copy=False)
+        torch.cuda.current_stream(self.device).synchronize()
+        return self._h_obs, self._h_reward, self._h_done
+
+    @property
+    def h2d_bytes_per_step(self) -> int:
+        return self.num_envs * (4 if self.discrete_actions else 8)
+
+    @property
+    def d2h_bytes_per_step(self) -> int:
+        return self.num_envs * (self.repeats * 14 * 4 + 4 + 1)
+
     # ---- device-side random-agent protocol (README.md:76-93) ----
     def rollout_random(self, n_steps: int, actions=(0, 1, 2, 3, 4)):
         if not self._was_reset:

@@ -198,6 +198,12 @@ int bcp_set_state(bcp_env* env, const double* host_buf, size_t n_doubles, void* 
  * bookkeeping) - bullet_cartpole.py:199 alone; used by single-substep parity. */
 int bcp_substep(bcp_env* env, void* stream);
 
+/* Measurement helper (bench.py only, no reference counterpart): dependent-free FFMA /
+ * DFMA chains on every SM for ~`iters` rounds; writes the achieved TFLOP/s
+ * (2 flops per FMA).  Gives the FP32 / FP64 CUDA-core pipe peak the roofline of this
+ * compute-bound path is quoted against (MEASURED_PEAKS.json has no such entry). */
+int bcp_bench_fma_peak(int device_ordinal, int use_f64, int iters, double* tflops_out);
+
 /* number of kernel launches this handle has enqueued (bench's gpu_launches) */
 int64_t bcp_launch_count(const bcp_env* env);
 
