@@ -38,7 +38,7 @@ def load(build_if_missing: bool = False):
     lib.bcp_destroy.argtypes = [vp]
     lib.bcp_reset.argtypes = [vp, vp, vp, vp]
     lib.bcp_step.argtypes = [vp, vp, vp, vp, vp, vp, vp]
-    lib.bcp_rollout_random.argtypes = [vp, i32, u32, vp, vp]
+    lib.bcp_rollout_random.argtypes = [vp, i32, u32, i32, vp, vp]
     lib.bcp_stats.argtypes = [vp, u64p, u64p, vp, vp]
     lib.bcp_stats_clear.argtypes = [vp, vp]
     lib.bcp_get_state.argtypes = [vp, vp, ctypes.c_size_t, vp]

@@ -16,16 +16,19 @@ from typing import Optional
 
 from . import urdf as _urdf
 
-BCP_ABI_VERSION = 4
+BCP_ABI_VERSION = 5
 DTYPE_F32, DTYPE_F64 = 0, 1
-REASON_NAMES = {0: None, 1: "out of position bounds", 2: "out of orientation bounds", 3: "episode length"}
+REASON_NAMES = {0: None, 1: "out of position bounds", 2: "out of orientation bounds", 3: "episode length",
+                4: "resetting", 5: "fresh"}
+REASON_RESETTING, REASON_FRESH = 4, 5
+AUTO_RESET_OFF, AUTO_RESET_PIPELINED = 0, 1
 FRAME_LINK, FRAME_WORLD = 0, 1
 THETA_PER_SUBSTEP, THETA_PER_RESET = 0, 1
 
 # canonical state record (include/bcp.h)
 S_CART, S_POLE, S_PEND_F, S_PEND_T, S_MANI = 0, 13, 26, 29, 32
 MANI_POINT, MANI_STRIDE, S_MANI_CNT = 11, 44, 164
-S_STEPS, S_DONE, S_EPISODE, STATE_DOUBLES = 167, 168, 169, 176
+S_STEPS, S_DONE, S_EPISODE, S_RESET_LEFT, STATE_DOUBLES = 167, 168, 169, 170, 176
 STATS_HEADER = 4
 
 
@@ -64,7 +67,7 @@ class BcpConfig(ctypes.Structure):
         ("force_frame", ctypes.c_int32),
         ("termination_enabled", ctypes.c_int32),
         ("carry_over_reset", ctypes.c_int32),
-        ("reserved0", ctypes.c_int32),
+        ("auto_reset", ctypes.c_int32),
         ("action_force", ctypes.c_double),
         ("initial_force", ctypes.c_double),
         ("pos_threshold", ctypes.c_double),
@@ -186,6 +189,10 @@ def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dt
     c.force_frame = FRAME_WORLD if g("world_frame_force", False) else FRAME_LINK
     c.termination_enabled = 0 if g("no_termination", False) else 1
     c.carry_over_reset = 0 if g("no_carry_over_reset", False) else 1
+    ar = g("auto_reset", "off")
+    if ar not in ("off", "pipelined"):
+        raise ValueError(f"auto_reset must be 'off' or 'pipelined', got {ar!r}")
+    c.auto_reset = AUTO_RESET_PIPELINED if ar == "pipelined" else AUTO_RESET_OFF
     c.action_force = float(opts.action_force)
     c.initial_force = float(opts.initial_force)
     c.pos_threshold = POS_THRESHOLD

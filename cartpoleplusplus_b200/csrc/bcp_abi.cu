@@ -69,6 +69,7 @@ int validate(const bcp_config* c) {
   if (c->dtype != BCP_DTYPE_F32 && c->dtype != BCP_DTYPE_F64) return fail("bcp_create: bad dtype");
   if (c->action_repeats < 1 || c->steps_per_repeat < 1 || c->max_episode_len < 1)
     return fail("bcp_create: action_repeats, steps_per_repeat, max_episode_len must be >= 1");
+  if (c->auto_reset != BCP_AUTO_RESET_OFF && c->auto_reset != BCP_AUTO_RESET_PIPELINED) return fail("bcp_create: bad auto_reset");
   if (c->friction_dirs != 1 && c->friction_dirs != 2) return fail("bcp_create: friction_dirs must be 1 or 2");
   if (c->solver_iterations < 1) return fail("bcp_create: solver_iterations must be >= 1");
   if (!(c->dt > 0)) return fail("bcp_create: dt must be > 0");
@@ -172,15 +173,16 @@ int bcp_substep(bcp_env* h, void* stream) {
   return 0;
 }
 
-int bcp_rollout_random(bcp_env* h, int32_t n_steps, uint32_t action_set_mask, float* obs_out, void* stream) {
+int bcp_rollout_random(bcp_env* h, int32_t n_steps, uint32_t action_set_mask, int32_t max_episodes, float* obs_out,
+                       void* stream) {
   if (!h) return fail("bcp_rollout_random: null handle");
-  if (n_steps < 0) return fail("bcp_rollout_random: n_steps < 0");
+  if (n_steps < 0 || max_episodes < 0) return fail("bcp_rollout_random: n_calls < 0 or max_episodes < 0");
   if (h->cfg.discrete_actions && (action_set_mask & 0x1fu) == 0) return fail("bcp_rollout_random: empty action set");
   if (n_steps == 0) return 0;
   DeviceGuard g(h->cfg.device_ordinal);
   cudaStream_t s = (cudaStream_t)stream;
-  if (h->f64()) CK(bcp::Launch<double>::rollout(h->p64, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, obs_out, h->stats(), s));
-  else CK(bcp::Launch<float>::rollout(h->p32, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, obs_out, h->stats(), s));
+  if (h->f64()) CK(bcp::Launch<double>::rollout(h->p64, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
+  else CK(bcp::Launch<float>::rollout(h->p32, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
   h->launches++;
   return 0;
 }

@@ -176,11 +176,20 @@ template <typename T> BCP_HD void apply_cart_force(const Params<T>& P, Env<T>& s
 }
 
 // state_fields_of_pose_of(cart), (pole) -> state[r] - bullet_cartpole.py:43-45,307-311
+// `o` is 8-byte aligned (14 floats per (repeat, env) block): seven float2 stores.
 template <typename T> BCP_HD void write_obs(const Env<T>& st, float* o) {
-  for (int i = 0; i < 3; ++i) o[i] = (float)st.cart.x[i];
-  for (int i = 0; i < 4; ++i) o[3 + i] = (float)st.cart.q[i];
-  for (int i = 0; i < 3; ++i) o[7 + i] = (float)st.pole.x[i];
-  for (int i = 0; i < 4; ++i) o[10 + i] = (float)st.pole.q[i];
+  float v[14];
+  for (int i = 0; i < 3; ++i) v[i] = (float)st.cart.x[i];
+  for (int i = 0; i < 4; ++i) v[3 + i] = (float)st.cart.q[i];
+  for (int i = 0; i < 3; ++i) v[7 + i] = (float)st.pole.x[i];
+  for (int i = 0; i < 4; ++i) v[10 + i] = (float)st.pole.q[i];
+#if defined(__CUDA_ARCH__)
+  float2* o2 = reinterpret_cast<float2*>(o);
+#pragma unroll
+  for (int i = 0; i < 7; ++i) o2[i] = make_float2(v[2 * i], v[2 * i + 1]);
+#else
+  for (int i = 0; i < 14; ++i) o[i] = v[i];
+#endif
 }
 
 // termination rule of bullet_cartpole.py:243-257, evaluated trig-free

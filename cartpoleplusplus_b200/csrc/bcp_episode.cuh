@@ -28,19 +28,35 @@ template <typename T> BCP_HD void push_force(const Params<T>& P, int64_t genv, i
   sincos_2pi(u24<T>(r.v[0]), ts, tc);
 }
 
-// BulletCartpole.reset - bullet_cartpole.py:313-346
-template <typename T, bool FRICTION>
-BCP_HD void env_reset(const Params<T>& P, Env<T>& st, int64_t genv) {
-  reset_begin(P, st);
-  for (int k = 0; k < P.settle_steps; ++k) substep<T, FRICTION>(P, st, nullptr);  // :326-327
-  T ts = 0, tc = 1;
-  if (P.theta_mode == BCP_THETA_PER_RESET) push_force(P, genv, st.episode, 0, ts, tc);
-  for (int k = 0; k < P.push_steps; ++k) {  // :329-332
-    substep<T, FRICTION>(P, st, nullptr);
-    if (P.theta_mode == BCP_THETA_PER_SUBSTEP) push_force(P, genv, st.episode, k, ts, tc);
-    apply_cart_force(P, st, P.initial_force * tc, P.initial_force * ts);
+// The substep a per-env program runs: StepParity (bcp_env.cuh substep<>, bit-exact with the
+// oracle in fp64) or StepFast (bcp_fast.cuh).  Programs below are templated on it.
+// Every program is entered by ALL lanes of a warp and calls the substep the same number of
+// times in each of them (`on` == false: the lane has no work; the fast path needs the whole
+// warp at its votes).
+template <typename T, bool FRICTION> struct StepParity {
+  BCP_HD void operator()(const Params<T>& P, Env<T>& st, bool on) const {
+    if (on) substep<T, FRICTION>(P, st, nullptr);
   }
-  st.episode += 1;
+};
+
+// BulletCartpole.reset - bullet_cartpole.py:313-346
+template <typename T, typename STEP>
+BCP_HD void env_reset(const Params<T>& P, Env<T>& st, int64_t genv, const STEP& sub, bool on) {
+  if (on) {
+    reset_begin(P, st);
+    st.reset_left = 0;
+  }
+  for (int k = 0; k < P.settle_steps; ++k) sub(P, st, on);  // :326-327
+  T ts = 0, tc = 1;
+  if (on && P.theta_mode == BCP_THETA_PER_RESET) push_force(P, genv, st.episode, 0, ts, tc);
+  for (int k = 0; k < P.push_steps; ++k) {  // :329-332
+    sub(P, st, on);
+    if (on) {
+      if (P.theta_mode == BCP_THETA_PER_SUBSTEP) push_force(P, genv, st.episode, k, ts, tc);
+      apply_cart_force(P, st, P.initial_force * tc, P.initial_force * ts);
+    }
+  }
+  if (on) st.episode += 1;
 }
 
 // action -> (fx, fy): discrete table (documented at :84,89; README.md:58) or
@@ -59,21 +75,71 @@ template <typename T> BCP_HD void action_force(const Params<T>& P, int a_disc, f
 }
 
 // BulletCartpole.step for a live env - bullet_cartpole.py:197-260.  `obs` points at
-// this env's (R,2,7) block with element stride `obs_stride` floats between
-// consecutive values (1 for a dense block; lets kernels stage through shared memory).
-template <typename T, bool FRICTION>
-BCP_HD int env_step(const Params<T>& P, Env<T>& st, T fx, T fy, float* obs) {
+// this env's dense (R,2,7) block (or nullptr).
+template <typename T, typename STEP>
+BCP_HD int env_step(const Params<T>& P, Env<T>& st, T fx, T fy, float* obs, const STEP& sub, bool on) {
   for (int r = 0; r < P.R; ++r) {    // :197
     for (int s = 0; s < P.S; ++s) {  // :198
-      substep<T, FRICTION>(P, st, nullptr);  // :199
-      apply_cart_force(P, st, fx, fy);       // :201-203
+      sub(P, st, on);                           // :199
+      if (on) apply_cart_force(P, st, fx, fy);  // :201-203
     }
-    if (obs) write_obs(st, obs + 14 * r);    // :237
+    if (on && obs) write_obs(st, obs + 14 * r);  // :237
   }
+  if (!on) return BCP_REASON_NONE;
   st.steps += 1;  // :239
   const int reason = done_reason(P, st);
   if (reason != BCP_REASON_NONE) st.done = 1;
   return reason;
+}
+
+// One call of the pipelined auto-reset machine (BCP_AUTO_RESET_PIPELINED): every env runs
+// exactly R*S substeps of whatever it is doing, so a warp never waits on a lane's reset.
+//   live env      : BulletCartpole.step as above (reward 1)
+//   done env      : enters its reset - teleport (:319-320) now, then the 100 settle and 30
+//                   push substeps (:326-332) R*S per call - and reports RESETTING
+//   reset finishes: observation bootstrap (:338-339) at the end of that call, FRESH
+// Returns the reason code; `live` tells whether this call was an env.step (reward 1).
+template <typename T, typename STEP>
+BCP_HD int env_advance(const Params<T>& P, Env<T>& st, int64_t genv, T fx, T fy, float* obs, const STEP& sub,
+                       bool on, bool& live) {
+  live = on && !st.done;
+  bool fresh = false;
+  if (on && st.done && st.reset_left == 0) {  // episode ended in an earlier call: reset starts
+    reset_begin(P, st);
+    st.done = 1;
+    st.reset_left = P.settle_steps + P.push_steps;
+    if (st.reset_left == 0) { st.done = 0; st.episode += 1; fresh = true; }
+  }
+  for (int r = 0; r < P.R; ++r) {
+    for (int s = 0; s < P.S; ++s) {
+      const bool resetting = on && !live && st.reset_left > 0;
+      sub(P, st, live || resetting);
+      if (live) {
+        apply_cart_force(P, st, fx, fy);
+      } else if (resetting) {
+        const int k = (P.settle_steps + P.push_steps) - st.reset_left - P.settle_steps;  // push index
+        if (k >= 0) {
+          T ts, tc;
+          push_force(P, genv, st.episode, (P.theta_mode == BCP_THETA_PER_SUBSTEP) ? k : 0, ts, tc);
+          apply_cart_force(P, st, P.initial_force * tc, P.initial_force * ts);
+        }
+        if (--st.reset_left == 0) { st.done = 0; st.episode += 1; fresh = true; }
+      }
+    }
+    if (live && obs) write_obs(st, obs + 14 * r);
+  }
+  if (!on) return BCP_REASON_NONE;
+  if (live) {
+    st.steps += 1;
+    const int reason = done_reason(P, st);
+    if (reason != BCP_REASON_NONE) st.done = 1;
+    return reason;
+  }
+  if (fresh) {
+    if (obs) for (int r = 0; r < P.R; ++r) write_obs(st, obs + 14 * r);
+    return BCP_REASON_FRESH;
+  }
+  return BCP_REASON_RESETTING;
 }
 
 // random-agent action draw (README.md:76-93 protocols), Philox keyed by global env id

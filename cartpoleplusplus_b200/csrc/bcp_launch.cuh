@@ -20,8 +20,8 @@ template <typename T> struct Launch {
   static cudaError_t reset(const Params<T>& P, void* f, int* id, const int* list, const int* count, int max_count,
                            float* obs, cudaStream_t s);
   static cudaError_t substep(const Params<T>& P, void* f, int* id, cudaStream_t s);
-  static cudaError_t rollout(const Params<T>& P, void* f, int* id, int n_steps, uint32_t action_mask, float* obs,
-                             StatsPtrs stats, cudaStream_t s);
+  static cudaError_t rollout(const Params<T>& P, void* f, int* id, int n_calls, uint32_t action_mask,
+                             int max_episodes, float* obs, StatsPtrs stats, cudaStream_t s);
   static cudaError_t export_state(int n, const void* f, const int* id, double* out, cudaStream_t s);
   static cudaError_t import_state(int n, void* f, int* id, const double* in, cudaStream_t s);
 };

@@ -10,8 +10,8 @@
 
 namespace bcp {
 
-enum { NF = BCP_S_MANI + 3 * BCP_MANI_STRIDE, NI = 6 };  // 164 scalars + cnt[3], steps, done, episode
-enum { I_CNT = 0, I_STEPS = 3, I_DONE = 4, I_EPISODE = 5 };
+enum { NF = BCP_S_MANI + 3 * BCP_MANI_STRIDE, NI = 7 };  // 164 scalars + cnt[3], steps, done, episode, reset_left
+enum { I_CNT = 0, I_STEPS = 3, I_DONE = 4, I_EPISODE = 5, I_RESET_LEFT = 6 };
 
 template <typename T> BCP_HD void load_body(const T* __restrict__ f, size_t N, size_t e, int base, Body<T>& b) {
   for (int i = 0; i < 3; ++i) b.x[i] = f[(size_t)(base + i) * N + e];
@@ -46,6 +46,7 @@ BCP_HD void load_env(const T* __restrict__ f, const int* __restrict__ id, size_t
   st.steps = id[(size_t)I_STEPS * N + e];
   st.done = id[(size_t)I_DONE * N + e];
   st.episode = id[(size_t)I_EPISODE * N + e];
+  st.reset_left = id[(size_t)I_RESET_LEFT * N + e];
 }
 template <typename T>
 BCP_HD void store_env(T* __restrict__ f, int* __restrict__ id, size_t N, size_t e, const Env<T>& st) {
@@ -67,6 +68,7 @@ BCP_HD void store_env(T* __restrict__ f, int* __restrict__ id, size_t N, size_t 
   id[(size_t)I_STEPS * N + e] = st.steps;
   id[(size_t)I_DONE * N + e] = st.done;
   id[(size_t)I_EPISODE * N + e] = st.episode;
+  id[(size_t)I_RESET_LEFT * N + e] = st.reset_left;
 }
 
 // canonical record (doubles, include/bcp.h) <-> register image
@@ -75,7 +77,7 @@ template <typename T> BCP_HD void env_from_canonical(const double* s, Env<T>& st
   for (int i = 0; i < NF; ++i) tmp[i] = (T)s[i];
   int cnt[3];
   for (int m = 0; m < 3; ++m) cnt[m] = (int)s[BCP_S_MANI_CNT + m];
-  const int ids[NI] = {cnt[0], cnt[1], cnt[2], (int)s[BCP_S_STEPS], (int)s[BCP_S_DONE], (int)s[BCP_S_EPISODE]};
+  const int ids[NI] = {cnt[0], cnt[1], cnt[2], (int)s[BCP_S_STEPS], (int)s[BCP_S_DONE], (int)s[BCP_S_EPISODE], (int)s[BCP_S_RESET_LEFT]};
   load_env<T>(tmp, ids, 1, 0, st);
 }
 template <typename T> BCP_HD void env_to_canonical(const Env<T>& st, double* s) {
@@ -88,7 +90,8 @@ template <typename T> BCP_HD void env_to_canonical(const Env<T>& st, double* s) 
   s[BCP_S_STEPS] = ids[I_STEPS];
   s[BCP_S_DONE] = ids[I_DONE];
   s[BCP_S_EPISODE] = ids[I_EPISODE];
-  for (int i = BCP_S_EPISODE + 1; i < BCP_STATE_DOUBLES; ++i) s[i] = 0.0;
+  s[BCP_S_RESET_LEFT] = ids[I_RESET_LEFT];
+  for (int i = BCP_S_RESET_LEFT + 1; i < BCP_STATE_DOUBLES; ++i) s[i] = 0.0;
 }
 
 }  // namespace bcp

@@ -25,6 +25,7 @@ template <typename T> struct Env {
   T pend_f[3], pend_t[3];  // external force/torque waiting for the next stepSimulation
   Manifold<T> mani[3];     // BCP_PAIR_* order
   int steps, done, episode;
+  int reset_left;  // pipelined auto-reset: reset substeps still to run (0 = not resetting)
 };
 
 template <typename T> struct BoxP {
@@ -43,11 +44,14 @@ template <typename T> struct Params {
   T pos_thr, sin_thr, tan_thr;
   int solver_iterations, friction_dirs, cone_friction, manifold_order, gyro_term;
   int discrete, R, S, max_len, push_steps, settle_steps;
-  int random_theta, theta_mode, force_frame, termination, carry_over;
+  int random_theta, theta_mode, force_frame, termination, carry_over, auto_reset;
   int num_envs;
   int64_t env_id_offset;
   uint64_t seed;
   bool any_friction;
+  // fast-mode row column layout (bcp_fast.cuh): per pair, rows per contact (1 normal +
+  // friction rows when the pair has friction) and the first word of the pair's rows
+  int rows_per_contact[3], row_base[3], col_words;
 };
 
 // ---- host-side conversion (plain host functions; never called from device code) ----
@@ -114,9 +118,16 @@ template <typename T> inline Params<T> make_params(const bcp_config& c) {
   p.force_frame = c.force_frame;
   p.termination = c.termination_enabled;
   p.carry_over = c.carry_over_reset;
+  p.auto_reset = c.auto_reset;
   p.num_envs = c.num_envs;
   p.env_id_offset = c.env_id_offset;
   p.seed = c.seed;
+  p.col_words = 0;
+  for (int m = 0; m < 3; ++m) {
+    p.rows_per_contact[m] = (p.mu[m] != T(0.0)) ? 1 + c.friction_dirs : 1;
+    p.row_base[m] = p.col_words;
+    p.col_words += 4 * p.rows_per_contact[m] * (m == BCP_PAIR_CART_POLE ? 13 : 10);
+  }
   return p;
 }
 

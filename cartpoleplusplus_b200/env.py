@@ -157,7 +157,10 @@ class BatchedBulletCartpole:
         return self.num_envs * (self.repeats * 14 * 4 + 4 + 1)
 
     # ---- device-side random-agent protocol (README.md:76-93) ----
-    def rollout_random(self, n_steps: int, actions=(0, 1, 2, 3, 4)):
+    def rollout_random(self, n_calls: int, actions=(0, 1, 2, 3, 4), max_episodes: int = 0):
+        """n_calls rounds of R*S substeps per env in one launch, actions drawn in-kernel; finished
+        episodes go to the histogram and reset in place (pipelined).  max_episodes > 0: an env
+        idles after that many episodes (protocol runs of a fixed number of episodes)."""
         if not self._was_reset:
             self.reset(copy=False)
         mask = 0
@@ -165,7 +168,8 @@ class BatchedBulletCartpole:
             if not 0 <= int(a) <= 4:
                 raise ValueError("discrete actions are 0..4")
             mask |= 1 << int(a)
-        _lib.check(self._lib.bcp_rollout_random(self._h, int(n_steps), mask, ctypes.c_void_p(self.obs.data_ptr()),
+        _lib.check(self._lib.bcp_rollout_random(self._h, int(n_calls), mask, int(max_episodes),
+                                                ctypes.c_void_p(self.obs.data_ptr()),
                                                 self._stream()), self._lib)
 
     def stats(self):

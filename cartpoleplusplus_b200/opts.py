@@ -37,6 +37,9 @@ def add_opts(parser: argparse.ArgumentParser) -> None:
                         help="physics arithmetic: fp32 fast mode, fp64 parity mode")
     parser.add_argument("--seed", type=int, default=0)
     parser.add_argument("--device", type=int, default=0, help="CUDA device ordinal")
+    parser.add_argument("--auto-reset", type=str, default="off", choices=["off", "pipelined"],
+                        help="off: the reference - a done env stays done until reset(); pipelined: a done env "
+                             "runs its 130-substep reset R*S substeps per step() call (info['done_reason'] 4/5)")
     # --- semantic switches (fork vs upstream) ---
     parser.add_argument("--no-termination", action="store_true",
                         help="fork behaviour: only the episode-length rule ends an episode "

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define BCP_ABI_VERSION 4
+#define BCP_ABI_VERSION 5
 
 /* ---- dtype of the physics arithmetic ------------------------------------ */
 #define BCP_DTYPE_F32 0 /* fast mode                                          */
@@ -37,6 +37,19 @@ extern "C" {
 #define BCP_REASON_POSITION 1    /* 'out of position bounds'    :245-248 */
 #define BCP_REASON_ORIENTATION 2 /* 'out of orientation bounds' :249-253 */
 #define BCP_REASON_LENGTH 3      /* 'episode length'            :255-257 */
+/* pipelined auto-reset only (no reference counterpart; see bcp_config.auto_reset): */
+#define BCP_REASON_RESETTING 4   /* env is inside its 130-substep reset: obs untouched,
+                                    reward 0, done 1                                  */
+#define BCP_REASON_FRESH 5       /* reset finished in this call: obs = reset observation
+                                    (:338-339), reward 0, done 0                      */
+
+/* ---- what bcp_step does with an env that is done ------------------------- */
+#define BCP_AUTO_RESET_OFF 0       /* the reference: 'calling step after done????' -
+                                      old obs, reward 0, done 1 (:179-181); the caller
+                                      resets with bcp_reset(mask)                     */
+#define BCP_AUTO_RESET_PIPELINED 1 /* the env runs its reset (:313-346) R*S substeps per
+                                      bcp_step call, exactly as many substeps as a live
+                                      env, and reports RESETTING / FRESH meanwhile     */
 
 /* ---- applyExternalForce frame (bullet_cartpole.py:203 vs the remnant :352) */
 #define BCP_FRAME_LINK 0
@@ -78,7 +91,7 @@ typedef struct bcp_config {
   int32_t termination_enabled; /* the rule of :243-253 (commented out in the fork) */
   int32_t carry_over_reset;    /* 1: reset keeps the pending force and the contact
                                   caches exactly as pybullet does (:319-327)      */
-  int32_t reserved0;
+  int32_t auto_reset;          /* BCP_AUTO_RESET_* */
   double action_force;    /* --action-force :18 */
   double initial_force;   /* --initial-force :20 */
   double pos_threshold;   /* 3.0, :58 */
@@ -131,6 +144,7 @@ typedef struct bcp_config {
 #define BCP_S_STEPS 167
 #define BCP_S_DONE 168
 #define BCP_S_EPISODE 169  /* number of resets so far (RNG counter word) */
+#define BCP_S_RESET_LEFT 170 /* pipelined auto-reset: reset substeps still to run */
 #define BCP_STATE_DOUBLES 176
 
 /* manifold (collision pair) indices, in Bullet's pair-creation order */
@@ -172,14 +186,21 @@ int bcp_reset(bcp_env* env, const uint8_t* mask, float* obs_out, void* stream);
 int bcp_step(bcp_env* env, const void* actions, float* obs_out, float* reward_out,
              uint8_t* done_out, uint8_t* reason_out, void* stream);
 
-/* Random-agent protocol of README.md:76-93 run entirely on the device: n_steps
- * env.steps per env with actions drawn in-kernel (Philox4x32-10), finished
- * episodes recorded in the episode-length histogram and reset in place.
+/* Random-agent protocol of README.md:76-93 run entirely on the device, state in
+ * registers across the whole launch: n_calls rounds of R*S substeps per env with
+ * actions drawn in-kernel (Philox4x32-10 keyed by global env id, episode, step);
+ * an env that finishes records its episode length in the histogram and runs its
+ * reset (:313-346) in the following rounds, R*S substeps per round, so every lane
+ * of a warp executes one physics substep per iteration whatever its phase.
  *   action_set_mask : discrete only, bit a set => action a may be drawn
  *                     (--actions="0,1,2,3,4" == 0x1f)
- *   obs_out may be NULL                                                      */
-int bcp_rollout_random(bcp_env* env, int32_t n_steps, uint32_t action_set_mask,
-                       float* obs_out, void* stream);
+ *   max_episodes    : > 0: an env idles once it has finished that many episodes
+ *                     (the protocol's --num-eval split over the envs; makes the
+ *                     histogram independent of n_calls and of the sharding);
+ *                     0: no limit
+ *   obs_out may be NULL; else the envs' latest observation                  */
+int bcp_rollout_random(bcp_env* env, int32_t n_calls, uint32_t action_set_mask,
+                       int32_t max_episodes, float* obs_out, void* stream);
 
 /* Episode statistics accumulated on the device since the last clear:
  *   hist : host i64[max_episode_len+1], hist[L] = episodes that ended at length L

@@ -3,18 +3,38 @@
 // exact per-env program the CUDA kernels run against the C oracle without a GPU.  It is
 // not reachable from the package and is not a product fallback.
 #include <cstring>
-#include "../../cartpoleplusplus_b200/csrc/bcp_env.cuh"
+#include <vector>
+#include "../../cartpoleplusplus_b200/csrc/bcp_fast.cuh"
 #include "../../cartpoleplusplus_b200/csrc/bcp_state.cuh"
 
 using namespace bcp;
 
+// path selector of the harness: 0 = parity substep<>, 1 = fast substep_fast<> (its shared-memory
+// column is a plain host array here)
+static int g_fast = 0;
+template <typename T, bool F> struct HostStep {
+  mutable std::vector<T> buf;
+  int fast;
+  explicit HostStep(const Params<T>& P) : buf((size_t)P.col_words + 1), fast(g_fast) {}
+  void operator()(const Params<T>& P, Env<T>& st, bool on) const { if (on) run(P, st, nullptr); }
+  void run(const Params<T>& P, Env<T>& st, SubstepInfo* info) const {
+    if (fast) {
+      Col<T> col{buf.data(), 1};
+      substep_fast<T, F>(P, st, col, true, info);
+    } else {
+      substep<T, F>(P, st, info);
+    }
+  }
+};
+
 template <typename T, bool F>
 static void substep_all(const Params<T>& P, double* state, int n, int32_t* info_out) {
+  const HostStep<T, F> sub(P);
   for (int e = 0; e < n; ++e) {
     Env<T> st;
     SubstepInfo info;
     env_from_canonical<T>(state + (size_t)e * BCP_STATE_DOUBLES, st);
-    substep<T, F>(P, st, &info);
+    sub.run(P, st, &info);
     env_to_canonical<T>(st, state + (size_t)e * BCP_STATE_DOUBLES);
     if (info_out) {
       int32_t* o = info_out + (size_t)e * 6;
@@ -25,11 +45,12 @@ static void substep_all(const Params<T>& P, double* state, int n, int32_t* info_
 }
 template <typename T, bool F>
 static void reset_all(const Params<T>& P, double* state, int n, const uint8_t* mask, float* obs) {
+  const HostStep<T, F> sub(P);
   for (int e = 0; e < n; ++e) {
     if (mask && !mask[e]) continue;
     Env<T> st;
     env_from_canonical<T>(state + (size_t)e * BCP_STATE_DOUBLES, st);
-    env_reset<T, F>(P, st, P.env_id_offset + e);
+    env_reset(P, st, P.env_id_offset + e, sub, true);
     if (obs) for (int r = 0; r < P.R; ++r) write_obs(st, obs + ((size_t)e * P.R + r) * 14);
     env_to_canonical<T>(st, state + (size_t)e * BCP_STATE_DOUBLES);
   }
@@ -37,10 +58,12 @@ static void reset_all(const Params<T>& P, double* state, int n, const uint8_t* m
 template <typename T, bool F>
 static void step_all(const Params<T>& P, double* state, int n, const void* actions, float* obs, float* reward,
                      uint8_t* done, uint8_t* reason) {
+  const HostStep<T, F> sub(P);
+  const bool pipelined = P.auto_reset == BCP_AUTO_RESET_PIPELINED;
   for (int e = 0; e < n; ++e) {
     Env<T> st;
     env_from_canonical<T>(state + (size_t)e * BCP_STATE_DOUBLES, st);
-    if (st.done) {
+    if (st.done && !pipelined) {
       reward[e] = 0.0f; done[e] = 1; if (reason) reason[e] = 0;
       continue;
     }
@@ -49,8 +72,10 @@ static void step_all(const Params<T>& P, double* state, int n, const void* actio
     else { ax = ((const float*)actions)[2 * e]; ay = ((const float*)actions)[2 * e + 1]; }
     T fx, fy;
     action_force(P, a, ax, ay, fx, fy);
-    const int rs = env_step<T, F>(P, st, fx, fy, obs ? obs + (size_t)e * P.R * 14 : nullptr);
-    reward[e] = 1.0f; done[e] = (uint8_t)st.done; if (reason) reason[e] = (uint8_t)rs;
+    float* o = obs ? obs + (size_t)e * P.R * 14 : nullptr;
+    bool live = true;
+    const int rs = pipelined ? env_advance(P, st, P.env_id_offset + e, fx, fy, o, sub, true, live) : env_step(P, st, fx, fy, o, sub, true);
+    reward[e] = live ? 1.0f : 0.0f; done[e] = (uint8_t)st.done; if (reason) reason[e] = (uint8_t)rs;
     env_to_canonical<T>(st, state + (size_t)e * BCP_STATE_DOUBLES);
   }
 }
@@ -66,4 +91,6 @@ int hh_reset_f32(const bcp_config* cfg, double* s, int n, const uint8_t* m, floa
 int hh_step_f64(const bcp_config* cfg, double* s, int n, const void* a, float* obs, float* rw, uint8_t* dn, uint8_t* rs) { DISPATCH(double, (step_all<double, true>(P, s, n, a, obs, rw, dn, rs)), (step_all<double, false>(P, s, n, a, obs, rw, dn, rs))); return 0; }
 int hh_step_f32(const bcp_config* cfg, double* s, int n, const void* a, float* obs, float* rw, uint8_t* dn, uint8_t* rs) { DISPATCH(float, (step_all<float, true>(P, s, n, a, obs, rw, dn, rs)), (step_all<float, false>(P, s, n, a, obs, rw, dn, rs))); return 0; }
 size_t hh_config_size(void) { return sizeof(bcp_config); }
+void hh_set_fast(int on) { g_fast = on; }
+int hh_col_words(const bcp_config* cfg) { return make_params<float>(*cfg).col_words; }
 }
