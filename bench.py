@@ -1,10 +1,14 @@
 #!/usr/bin/env python
 """bench.py — env-steps/sec of the batched BulletCartpole step path on B200.
 
-A "step" is one `env.step` over the whole batch (BASELINE.json configs[2]: 65536 envs per
-GPU, continuous 2-D force, --action-force=100, uniform random actions, low-dim (R,2,7)
-obs) followed by the reset of the envs that finished (130 substeps each, compacted into
-dense warps).  Contract and JSON keys: see the task statement / DESIGN.md section 6.
+Workload (BASELINE.json configs[2]): 65536 envs per GPU, continuous 2-D force,
+--action-force=100, uniform random actions, low-dim (R,2,7) observations, the reference's
+own models and defaults otherwise (R=2, S=1, --initial-force=200, termination rule on).
+Envs auto-reset in the pipelined mode: a finished env runs its
+130-substep reset R*S substeps per call next to the live envs, so every reset substep is
+inside the timed region.  A bench "step" is one `env.step` over the whole batch; `value`
+counts only the env.steps actually taken (reward 1) - slots that are resetting do not count.
+Before timing, the batch is rolled to its stationary mix of episode phases (untimed).
 
   python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
   torchrun --nproc-per-node N bench.py --gpus N ...        (one rank per GPU, NCCL)
@@ -27,60 +31,77 @@ sys.path.insert(0, ROOT)
 from cartpoleplusplus_b200 import default_opts, make_config  # noqa: E402
 from cartpoleplusplus_b200 import config as C  # noqa: E402
 
-WORKLOAD = "configs[2]: 65536 envs/GPU, continuous 2-D force, action_force=100, U(-1,1)^2 actions, (R,2,7) obs"
+WORKLOAD = ("configs[2]: 65536 envs/GPU, continuous 2-D force, action_force=100, U(-1,1)^2 actions, "
+            "(R,2,7) obs, reference models/defaults")
 
 
-def workload_opts(args):
+def workload_opts(args, **extra):
     return default_opts(action_force=100.0, initial_force=args.initial_force, action_repeats=args.repeats,
-                        steps_per_repeat=args.steps_per_repeat)
+                        steps_per_repeat=args.steps_per_repeat, cart_friction=args.cart_friction, **extra)
 
 
 # ---------------------------------------------------------------------------------------
-# flop / byte model of one substep (FMA = 2 flops, useful work only)
+# flop model of the solve (FMA = 2 flops, useful work only: masked lanes,
+# padding and recomputation do not count).  One row update / one cone update of two rows.
 # ---------------------------------------------------------------------------------------
-F_FIXED = 2400.0        # poses->matrices, 2x forward dynamics, 3x SAT (+clip), manifolds, 2x integrate
-F_SETUP_2, F_SETUP_1 = 250.0, 150.0   # contact-row setup: two dynamic bodies / one
-F_SWEEP_2, F_SWEEP_1 = 60.0, 36.0     # one PGS row update: two dynamic bodies / one
+F_ROW1, F_ROW2 = 36.0, 61.0      # normal row touching one / two dynamic bodies
+F_CONE1, F_CONE2 = 83.0, 133.0   # the two friction rows of one contact, cone-clipped
 
 
-def flops_per_substep(rows_cart_pole, rows_ground, iters):
-    return (F_FIXED + rows_cart_pole * F_SETUP_2 + rows_ground * F_SETUP_1
-            + iters * (rows_cart_pole * F_SWEEP_2 + rows_ground * F_SWEEP_1))
+def solve_flops(info, cfg):
+    """Useful flops of the PGS solve of one substep for the envs censused in `info`
+    (oracle substep info rows: iterations, rows, friction rows, contacts gc/cp/gp)."""
+    it = info[:, 0].astype(np.float64)
+    gc, cp, gp = (info[:, 3 + k].astype(np.float64) for k in range(3))
+    mu = {"gc": cfg.ground.friction * cfg.cart.friction, "cp": cfg.cart.friction * cfg.pole.friction,
+          "gp": cfg.ground.friction * cfg.pole.friction}
+    per_iter = gc * F_ROW1 + gp * F_ROW1 + cp * F_ROW2
+    if cfg.friction_dirs == 2:
+        per_iter += (gc * F_CONE1 if mu["gc"] else 0) + (gp * F_CONE1 if mu["gp"] else 0) + (cp * F_CONE2 if mu["cp"] else 0)
+    return it * per_iter
 
 
-def bytes_per_env_step(cfg, mean_points):
-    """Algorithmic HBM bytes of one env.step launch per env: state in + out, action, obs, flags."""
-    sz = 8 if cfg.dtype == C.DTYPE_F64 else 4
-    state = (32 + mean_points * C.MANI_POINT) * sz + 6 * 4
-    act = 4 if cfg.discrete_actions else 8
-    return 2 * state + act + cfg.action_repeats * 56 + 4 + 1 + 1
+def solve_bytes(info, cfg):
+    """Algorithmic bytes one solve moves per env: the live rows of its record in, the
+    velocity deltas, iteration count and normal impulses out (fp32)."""
+    gc, cp, gp = (info[:, 3 + k].astype(np.float64) for k in range(3))
+    rpc = lambda a, b: 3 if (a * b) and cfg.friction_dirs == 2 else 1  # noqa: E731
+    words = (gc * rpc(cfg.ground.friction, cfg.cart.friction) * 10 + gp * rpc(cfg.ground.friction, cfg.pole.friction) * 10
+             + cp * rpc(cfg.cart.friction, cfg.pole.friction) * 13)
+    return 4.0 * (words + 16 + 13 + (gc + cp + gp))
 
 
 # ---------------------------------------------------------------------------------------
 # CPU baseline: the oracle (a port - pybullet is unavailable on this box), all host threads
 # ---------------------------------------------------------------------------------------
-def cpu_baseline(args, steps=None, n_envs=None):
+def cpu_rollout(args, n_envs, n_steps, warm_steps):
+    """Oracle random-agent rollout with synchronous in-place resets: n_envs x n_steps env.steps
+    (+ the 130-substep resets they trigger), OpenMP over all host threads.  Same workload,
+    same action distribution, from the stationary phase mix."""
     from oracle import Oracle
-    cores = os.cpu_count() or 1
-    n = n_envs or 128 * cores
-    steps = steps or 12
-    opts = workload_opts(args)
-    cfg = make_config(opts, False, num_envs=n, dtype="fp64", seed=args.seed)
+    cfg = make_config(workload_opts(args), False, num_envs=n_envs, dtype="fp64", seed=args.seed)
     ora = Oracle(cfg, dtype="fp64")
-    rng = np.random.default_rng(args.seed)
-    ora.reset()
-    acts = rng.uniform(-1, 1, size=(steps, n, 2)).astype(np.float32)
+    ora.state[:, C.S_DONE] = 1  # rollout_random resets every env first
+    ora.rollout_random(warm_steps)
+    h0 = ora.header.copy()
     t0 = time.perf_counter()
-    resets = 0
-    for t in range(steps):
-        _, _, done, _ = ora.step(acts[t])
-        if done.any():
-            ora.reset(done.astype(np.uint8))
-            resets += int(done.sum())
+    ora.rollout_random(n_steps)
     dt = time.perf_counter() - t0
-    return {"value": n * steps / dt, "unit": "env-steps/s", "cores": cores, "kind": "port",
-            "sample": f"{n} envs x {steps} env.steps (+{resets} resets of 130 substeps) of the same workload, "
-                      f"fp64 C oracle, OpenMP over {cores} threads; pybullet: unavailable on this box",
+    steps = int(ora.header[1] - h0[1])
+    resets = int(ora.header[3] - h0[3])
+    return steps, resets, dt
+
+
+def cpu_baseline(args, budget_s=12.0):
+    cores = os.cpu_count() or 1
+    n = 256 * cores
+    steps, resets, dt = cpu_rollout(args, n, 8, 40)  # probe
+    rate = steps / dt
+    n_steps = int(max(8, min(4000, budget_s * rate / n)))
+    steps, resets, dt = cpu_rollout(args, n, n_steps, 40)
+    return {"value": steps / dt, "unit": "env-steps/s", "cores": cores, "kind": "port",
+            "sample": f"{n} envs x {n_steps} env.steps (+{resets} resets of 130 substeps) of the same workload from its "
+                      f"stationary phase mix, fp64 C oracle, OpenMP over {cores} threads; pybullet: unavailable on this box",
             "seconds": dt, "resets": resets}
 
 
@@ -103,7 +124,7 @@ class ClockSampler(threading.Thread):
                 self.rows.append([c.strip() for c in out.strip().split(",")])
             except Exception:
                 pass
-            time.sleep(0.1)
+            time.sleep(0.05)
 
     def summary(self):
         rows = [r for r in self.rows if len(r) >= 7]
@@ -120,6 +141,7 @@ class ClockSampler(threading.Thread):
 # the measured arm
 # ---------------------------------------------------------------------------------------
 def run_ours(args):
+    import ctypes
     import torch
     import torch.distributed as dist
     from cartpoleplusplus_b200 import _lib
@@ -133,15 +155,19 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     dev = torch.device("cuda", local)
     n = args.envs
-    opts = workload_opts(args)
+    opts = workload_opts(args, auto_reset="pipelined")
     env = BatchedBulletCartpole(opts, discrete_actions=False, num_envs=n, device=local, dtype=args.dtype,
                                 seed=args.seed, env_id_offset=rank * n)
     K, W = args.steps, args.warmup
+    RS = env.cfg.action_repeats * env.cfg.steps_per_repeat
     gen = torch.Generator(device=dev)
     gen.manual_seed(args.seed + rank)
     pool = torch.rand((W + K, n, 2), device=dev, generator=gen) * 2 - 1  # inputs resident in HBM
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > L2 (126 MB)
     env.reset(copy=False)
+    # untimed: roll the batch to its stationary mix of episode phases (random agent, in-kernel actions)
+    env.rollout_random(args.mix_calls)
+    torch.cuda.synchronize()
 
     def one_step(t, ev=None):
         flush.zero_()  # untimed L2 flush between steps
@@ -150,9 +176,6 @@ def run_ours(args):
         env.step(pool[t], copy=False)
         if ev:
             ev[1].record()
-        env.reset(mask=env.done, copy=False)
-        if ev:
-            ev[2].record()
 
     for t in range(W):
         one_step(t)
@@ -161,23 +184,22 @@ def run_ours(args):
     launches0 = env.launch_count
     sampler = ClockSampler(local)
     sampler.start()
+    env.profile_begin()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
-    wall0 = time.perf_counter()
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(K)]
     for t in range(K):
         one_step(W + t, evs[t])
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    wall = time.perf_counter() - wall0
     sampler.stop_flag = True
-    step_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
-    reset_ms = sum(e[1].elapsed_time(e[2]) for e in evs)
-    total_ms = step_ms + reset_ms
+    prof = env.profile_end()
+    total_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
     launches = env.launch_count - launches0
     hist, header, _ = env.stats()
+    live_steps = header["env_steps"]
 
     # ---- e2e: same metric through step_host (pinned host buffers, H2D + D2H inside) ----
     host_actions = [torch.empty((n, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
@@ -185,83 +207,100 @@ def run_ours(args):
         h.uniform_(-1, 1)
     Ke = max(3, min(K, 20))
     for t in range(2):
-        env.step_host(host_actions[t % 2], auto_reset=True)
+        env.step_host(host_actions[t % 2])
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    e2e_live = 0
     t0 = time.perf_counter()
     for t in range(Ke):
-        env.step_host(host_actions[t % 2], auto_reset=True)
+        _, rew, _ = env.step_host(host_actions[t % 2])
+        e2e_live += int(rew.sum().item())
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
 
-    # ---- max over ranks, whole-job aggregate; the one collective: histogram allreduce ----
-    tt = torch.tensor([total_ms, step_ms, reset_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    # ---- max over ranks of the times, sums of the counts; the one collective: statistics allreduce ----
+    tt = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
+    cc = torch.tensor([live_steps, e2e_live, header["episodes"]], dtype=torch.int64, device=dev)
     hist_t = torch.from_numpy(hist).to(dev)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        dist.all_reduce(cc, op=dist.ReduceOp.SUM)
         dist.all_reduce(hist_t, op=dist.ReduceOp.SUM)
-    total_ms, step_ms, reset_ms, e2e_ms = (float(v) for v in tt.tolist())
+    total_ms, e2e_ms = (float(v) for v in tt.tolist())
+    live_all, e2e_live_all, episodes_all = (int(v) for v in cc.tolist())
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel (k_step): flops from a sampled state census ----
+    # ---- roofline of the dominant kernel: census of a state sample through the oracle ----
     from oracle import Oracle
     ns = min(n, 4096)
     st = env.get_state()[:ns].copy()
+    busy = (st[:, C.S_DONE] == 0) | (st[:, C.S_RESET_LEFT] > 0)   # envs that run a substep next call
     st[:, C.S_DONE] = 0
     scfg = C.copy_config(env.cfg)
     scfg.num_envs = ns
     ora = Oracle(scfg, dtype="fp64")
     ora.state[:] = st
     info = ora.substep(with_info=True)
-    iters = float(info[:, 0].mean())
-    rows_gc, rows_cp, rows_gp = (float(info[:, 3 + k].mean()) for k in range(3))
-    f_sub = flops_per_substep(rows_cp, rows_gc + rows_gp, iters)
-    RS = env.cfg.action_repeats * env.cfg.steps_per_repeat
-    flops_launch = f_sub * RS * n
-    step_launch_ms = step_ms / K
+    info[~busy] = 0
+    iters = float(info[busy, 0].mean()) if busy.any() else 0.0
+    rows_gc, rows_cp, rows_gp = (float(info[busy, 3 + k].mean()) for k in range(3))
+    flops_env = float(solve_flops(info, env.cfg).mean())
+    bytes_env = float(solve_bytes(info, env.cfg).mean())
+    split = prof["n_solve"] > 0
+    dom_name = "k_solve" if split else "k_step"
+    dom_ms = (prof["ms_solve"] / max(1, prof["n_solve"])) if split else (prof["ms_prep"] / max(1, prof["n_prep"]))
+    flops_launch = flops_env * n * (1 if split else RS)
+    bytes_launch = bytes_env * n * (1 if split else RS)
     lib = _lib.load()
-    import ctypes
     peak32, peak64 = ctypes.c_double(), ctypes.c_double()
     lib.bcp_bench_fma_peak(local, 0, 4096, ctypes.byref(peak32))
     lib.bcp_bench_fma_peak(local, 1, 1024, ctypes.byref(peak64))
     pipe_peak = peak64.value if args.dtype == "fp64" else peak32.value
-    achieved_tf = flops_launch / (step_launch_ms * 1e-3) / 1e12
+    achieved_tf = flops_launch / (dom_ms * 1e-3) / 1e12
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    bytes_launch = bytes_per_env_step(env.cfg, rows_gc + rows_cp + rows_gp) * n
-    achieved_gbs = bytes_launch / (step_launch_ms * 1e-3) / 1e9
-    value = world * n * K / (total_ms * 1e-3)
+    achieved_gbs = bytes_launch / (dom_ms * 1e-3) / 1e9
+    value = live_all / (total_ms * 1e-3)
     out = {
         "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": total_ms / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32" if args.dtype == "fp32" else "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "envs_per_gpu": n, "action_repeats": env.cfg.action_repeats,
                    "steps_per_repeat": env.cfg.steps_per_repeat, "initial_force": args.initial_force,
-                   "termination": "angle/position/200-step rule on", "auto_reset": "compacted reset kernel per step",
+                   "cart_friction": env.cfg.cart.friction,
+                   "termination": "angle/position/200-step rule on",
+                   "auto_reset": "pipelined: a finished env runs its 130-substep reset R*S substeps per call; only env.steps "
+                                 "actually taken are counted",
+                   "phase_mix": f"stationary ({args.mix_calls} untimed random-agent calls before timing)",
                    "l2": "flushed between steps (256 MiB memset, untimed)", "parallelism": f"env-sharded x{world}",
                    "seed": args.seed},
-        "substeps_per_s": (world * n * K * RS + int(hist_t.sum().item()) * (env.cfg.settle_steps + env.cfg.initial_force_steps)) / (total_ms * 1e-3),
-        "step_kernel_ms": step_launch_ms, "reset_ms_per_step": reset_ms / K,
-        "episodes_finished": int(hist_t.sum().item()),
-        "e2e": {"value": world * n * Ke / (e2e_ms * 1e-3), "unit": "env-steps/s",
+        "live_fraction": live_all / (world * n * K),
+        "slot_steps_per_s": world * n * K / (total_ms * 1e-3),
+        "substeps_per_s": world * n * K * RS / (total_ms * 1e-3),
+        "episodes_finished": episodes_all,
+        "mean_episode_len": float((hist_t.cpu().numpy() * np.arange(len(hist))).sum() / max(1, int(hist_t.sum().item()))),
+        "kernel_ms_per_step": {"k_prep" if split else "k_step": prof["ms_prep"] / K, "k_solve": prof["ms_solve"] / K},
+        "e2e": {"value": e2e_live_all / (e2e_ms * 1e-3), "unit": "env-steps/s",
                 "h2d_bytes_per_step": env.h2d_bytes_per_step, "d2h_bytes_per_step": env.d2h_bytes_per_step},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved_gbs / hbm_peak, "traffic": None,
-                     "note": "schema-mandated HBM view of k_step; the kernel is FP32-pipe/latency bound, see roofline_pipe"},
-        "roofline_pipe": {"bound": "fp32-cuda-core" if args.dtype == "fp32" else "fp64-cuda-core",
+                     "frac": achieved_gbs / hbm_peak, "traffic": None, "kernel": dom_name,
+                     "note": "schema-mandated HBM view; the kernel is FP32-pipe / issue-latency bound, see roofline_pipe"},
+        "roofline_pipe": {"bound": "fp32-cuda-core" if args.dtype == "fp32" else "fp64-cuda-core", "kernel": dom_name,
+                          "launch_ms": dom_ms, "share_of_step": (prof["ms_solve"] if split else prof["ms_prep"]) / total_ms,
                           "achieved": achieved_tf, "peak": pipe_peak, "unit": "TFLOP/s", "frac": achieved_tf / pipe_peak,
                           "peak_source": "bcp_bench_fma_peak (FMA chains, measured in this run)",
-                          "flops_per_substep": f_sub, "mean_solver_iterations": iters,
+                          "flops_per_env_solve": flops_env, "bytes_per_env_solve": bytes_env,
+                          "mean_solver_iterations": iters, "busy_fraction": float(busy.mean()),
                           "mean_rows": {"ground_cart": rows_gc, "cart_pole": rows_cp, "ground_pole": rows_gp}},
     }
     if not args.no_cpu_baseline and world == 1:
@@ -273,31 +312,34 @@ def run_ours(args):
 
 def run_reference(args):
     """--impl reference: the reference's CPU path.  pybullet is unavailable on this box, so this
-    times the oracle port (the one other place bench.py may execute oracle/), all host threads."""
+    times the oracle port (the one other place bench.py may execute oracle/), all host threads.
+    Each bench step is a bounded sample: every env of a host-sized batch takes `per` env.steps."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     cores = os.cpu_count() or 1
     K, W = args.steps, args.warmup
-    n = 64 * cores
-    per = max(2, min(8, 200 // max(1, K + W)))  # env.steps per bench "step" (bounded sample)
-    vals = []
+    n = 256 * cores
+    probe_steps, _, probe_dt = cpu_rollout(args, n, 8, 40)
+    rate = probe_steps / probe_dt
+    per = int(max(2, min(200, 90.0 * rate / n / max(1, K + W))))  # whole run ~90 s of CPU work
+    tot_steps, tot_s, tot_resets = 0, 0.0, 0
     for t in range(W + K):
-        b = cpu_baseline(args, steps=per, n_envs=n)
+        steps, resets, dt = cpu_rollout(args, n, per, 40)
         if t >= W:
-            vals.append(b)
-    total_steps = sum(n * per for _ in vals)
-    total_s = sum(b["seconds"] for b in vals)
-    v = total_steps / total_s
+            tot_steps += steps
+            tot_s += dt
+            tot_resets += resets
+    v = tot_steps / tot_s
     print(json.dumps({
         "impl": "reference", "metric": "env-steps/sec", "value": v, "unit": "env-steps/s",
         "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": K, "warmup": W,
-        "ms_per_step": 1e3 * total_s / max(1, K), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": 1e3 * tot_s / max(1, K), "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "sample_envs": n, "env_steps_per_bench_step": per},
         "cpu_baseline": {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                         "sample": f"{n} envs x {per} env.steps per bench step incl. resets; C oracle (fp64, OpenMP); "
-                                   "pybullet: unavailable on this box"},
+                         "sample": f"{n} envs x {per} env.steps per bench step (+{tot_resets} resets of 130 substeps in all), "
+                                   "stationary phase mix; C oracle (fp64, OpenMP); pybullet: unavailable on this box"},
         "e2e": {"value": v, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -314,6 +356,8 @@ def main():
     ap.add_argument("--initial-force", type=float, default=200.0)
     ap.add_argument("--repeats", type=int, default=2)
     ap.add_argument("--steps-per-repeat", type=int, default=1)
+    ap.add_argument("--cart-friction", type=float, default=None, help="override cart.urdf's lateral_friction (0.0)")
+    ap.add_argument("--mix-calls", type=int, default=400, help="untimed random-agent calls before timing")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -2,6 +2,7 @@
 // No CPU implementation exists behind these entry points: without a CUDA device
 // bcp_create fails and nothing else can be called.
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <new>
 #include <string>
@@ -43,6 +44,11 @@ struct bcp_env {
   int* list = nullptr;   // compacted env indices for masked resets
   int* count = nullptr;
   double* staging = nullptr;  // canonical records for get/set_state
+  bcp::SplitBuffers split = {nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
+  int use_split = 0;
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_events;  // bracketing every kernel of bcp_step while profiling
+  std::vector<int> prof_calls;           // events per bcp_step call
   int64_t launches = 0;
   bool f64() const { return cfg.dtype == BCP_DTYPE_F64; }
   bcp::StatsPtrs stats() const { return bcp::StatsPtrs{hist, header, reward_sum}; }
@@ -118,6 +124,17 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
     std::vector<int> ones(N, 1);
     err = cudaMemcpy(h->idata + (size_t)bcp::I_DONE * N, ones.data(), N * sizeof(int), cudaMemcpyHostToDevice);
   }
+  // fp32 with enough envs to fill the machine: env.step runs as the split pipeline
+  // (BCP_SPLIT=0/1 overrides; the one-launch fast kernel is the alternative)
+  {
+    const char* sv = getenv("BCP_SPLIT");
+    h->use_split = (!h->f64()) && (sv ? atoi(sv) != 0 : cfg->num_envs >= 4096);
+    if (h->use_split) {
+      A((void**)&h->split.recs, bcp::split_record_words(h->p32) * N * sizeof(float));
+      A((void**)&h->split.queue, N * sizeof(int));
+      A((void**)&h->split.qc, bcp::split_counter_words(h->p32) * sizeof(int));
+    }
+  }
   if (err != cudaSuccess) {
     bcp_destroy(h);
     return fail("bcp_create: device allocation failed", err);
@@ -131,6 +148,7 @@ int bcp_destroy(bcp_env* h) {
   DeviceGuard g(h->cfg.device_ordinal);
   cudaFree(h->fdata); cudaFree(h->idata); cudaFree(h->hist); cudaFree(h->header);
   cudaFree(h->reward_sum); cudaFree(h->list); cudaFree(h->count); cudaFree(h->staging);
+  cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc);
   delete h;
   return 0;
 }
@@ -157,8 +175,20 @@ int bcp_step(bcp_env* h, const void* actions, float* obs_out, float* reward_out,
   if (!actions) return fail("bcp_step: null actions");
   DeviceGuard g(h->cfg.device_ordinal);
   cudaStream_t s = (cudaStream_t)stream;
+  if (!h->f64() && h->use_split) {
+    int n = 0;
+    const size_t ev0 = h->prof_events.size();
+    CK(bcp::launch_step_split(h->p32, (float*)h->fdata, h->idata, h->split, actions, obs_out, reward_out, done_out, reason_out, h->stats(), s, &n,
+                              h->profiling ? &h->prof_events : nullptr));
+    if (h->profiling) h->prof_calls.push_back((int)(h->prof_events.size() - ev0));
+    h->launches += n;
+    return 0;
+  }
+  cudaEvent_t e0 = nullptr, e1 = nullptr;
+  if (h->profiling) { cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventRecord(e0, s); }
   if (h->f64()) CK(bcp::Launch<double>::step(h->p64, h->fdata, h->idata, actions, obs_out, reward_out, done_out, reason_out, h->stats(), s));
   else CK(bcp::Launch<float>::step(h->p32, h->fdata, h->idata, actions, obs_out, reward_out, done_out, reason_out, h->stats(), s));
+  if (h->profiling) { cudaEventRecord(e1, s); h->prof_events.push_back(e0); h->prof_events.push_back(e1); h->prof_calls.push_back(2); }
   h->launches++;
   return 0;
 }
@@ -181,8 +211,11 @@ int bcp_rollout_random(bcp_env* h, int32_t n_steps, uint32_t action_set_mask, in
   if (n_steps == 0) return 0;
   DeviceGuard g(h->cfg.device_ordinal);
   cudaStream_t s = (cudaStream_t)stream;
-  if (h->f64()) CK(bcp::Launch<double>::rollout(h->p64, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
-  else CK(bcp::Launch<float>::rollout(h->p32, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
+  bcp::Params<double> p64 = h->p64;
+  bcp::Params<float> p32 = h->p32;
+  p64.auto_reset = p32.auto_reset = BCP_AUTO_RESET_PIPELINED;  // a rollout resets its envs in place
+  if (h->f64()) CK(bcp::Launch<double>::rollout(p64, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
+  else CK(bcp::Launch<float>::rollout(p32, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
   h->launches++;
   return 0;
 }
@@ -252,5 +285,39 @@ int bcp_bench_fma_peak(int device_ordinal, int use_f64, int iters, double* tflop
 }
 
 int64_t bcp_launch_count(const bcp_env* h) { return h ? h->launches : 0; }
+
+int bcp_profile_begin(bcp_env* h) {
+  if (!h) return fail("bcp_profile_begin: null handle");
+  for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
+  h->prof_events.clear();
+  h->prof_calls.clear();
+  h->profiling = true;
+  return 0;
+}
+
+int bcp_profile_end(bcp_env* h, double* out4) {
+  if (!h || !out4) return fail("bcp_profile_end: null argument");
+  DeviceGuard g(h->cfg.device_ordinal);
+  h->profiling = false;
+  double ms[2] = {0, 0};
+  long long cnt[2] = {0, 0};
+  size_t at = 0;
+  for (int n : h->prof_calls) {
+    // n events bracket n-1 kernels: k_prep, k_solve, k_prep, ... (split) or one kernel
+    for (int k = 0; k + 1 < n; ++k) {
+      CK(cudaEventSynchronize(h->prof_events[at + k + 1]));
+      float t = 0;
+      CK(cudaEventElapsedTime(&t, h->prof_events[at + k], h->prof_events[at + k + 1]));
+      ms[k & 1] += t;
+      cnt[k & 1]++;
+    }
+    at += n;
+  }
+  for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);
+  h->prof_events.clear();
+  h->prof_calls.clear();
+  out4[0] = ms[0]; out4[1] = ms[1]; out4[2] = (double)cnt[0]; out4[3] = (double)cnt[1];
+  return 0;
+}
 
 }  // extern "C"

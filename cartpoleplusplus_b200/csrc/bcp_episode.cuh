@@ -74,72 +74,77 @@ template <typename T> BCP_HD void action_force(const Params<T>& P, int a_disc, f
   }
 }
 
-// BulletCartpole.step for a live env - bullet_cartpole.py:197-260.  `obs` points at
-// this env's dense (R,2,7) block (or nullptr).
-template <typename T, typename STEP>
-BCP_HD int env_step(const Params<T>& P, Env<T>& st, T fx, T fy, float* obs, const STEP& sub, bool on) {
-  for (int r = 0; r < P.R; ++r) {    // :197
-    for (int s = 0; s < P.S; ++s) {  // :198
-      sub(P, st, on);                           // :199
-      if (on) apply_cart_force(P, st, fx, fy);  // :201-203
-    }
-    if (on && obs) write_obs(st, obs + 14 * r);  // :237
-  }
-  if (!on) return BCP_REASON_NONE;
-  st.steps += 1;  // :239
-  const int reason = done_reason(P, st);
-  if (reason != BCP_REASON_NONE) st.done = 1;
-  return reason;
-}
-
-// One call of the pipelined auto-reset machine (BCP_AUTO_RESET_PIPELINED): every env runs
-// exactly R*S substeps of whatever it is doing, so a warp never waits on a lane's reset.
-//   live env      : BulletCartpole.step as above (reward 1)
-//   done env      : enters its reset - teleport (:319-320) now, then the 100 settle and 30
-//                   push substeps (:326-332) R*S per call - and reports RESETTING
+// ---- one call of an env, in pieces ------------------------------------------------------
+// BulletCartpole.step (bullet_cartpole.py:178-275) and the pipelined auto-reset machine
+// (BCP_AUTO_RESET_PIPELINED) share one shape: decide what the env does during this call,
+// run R*S substeps with a little work after each, close the call.  The pieces are used by
+// the one-launch programs below and, one kernel per piece, by the split pipeline
+// (bcp_split.cuh).
+//   live env      : [stepSimulation; applyExternalForce] x S, pose capture, x R  (reward 1)
+//   done env      : reference: nothing (:179-181).  Pipelined: enters its reset - teleport
+//                   (:319-320) now, then the 100 settle and 30 push substeps (:326-332) R*S per
+//                   call, so that a warp never waits on one lane's reset - and reports RESETTING
 //   reset finishes: observation bootstrap (:338-339) at the end of that call, FRESH
-// Returns the reason code; `live` tells whether this call was an env.step (reward 1).
-template <typename T, typename STEP>
-BCP_HD int env_advance(const Params<T>& P, Env<T>& st, int64_t genv, T fx, T fy, float* obs, const STEP& sub,
-                       bool on, bool& live) {
-  live = on && !st.done;
-  bool fresh = false;
-  if (on && st.done && st.reset_left == 0) {  // episode ended in an earlier call: reset starts
+enum { MODE_IDLE = 0, MODE_LIVE = 1, MODE_RESET = 2, MODE_FRESH = 3 };
+
+template <typename T> BCP_HD int call_begin(const Params<T>& P, Env<T>& st, bool valid) {
+  if (!valid) return MODE_IDLE;
+  if (!st.done) return MODE_LIVE;
+  if (P.auto_reset != BCP_AUTO_RESET_PIPELINED) return MODE_IDLE;
+  if (st.reset_left == 0) {  // episode ended in an earlier call: the reset starts
     reset_begin(P, st);
     st.done = 1;
     st.reset_left = P.settle_steps + P.push_steps;
-    if (st.reset_left == 0) { st.done = 0; st.episode += 1; fresh = true; }
+    if (st.reset_left == 0) { st.done = 0; st.episode += 1; return MODE_FRESH; }
   }
-  for (int r = 0; r < P.R; ++r) {
-    for (int s = 0; s < P.S; ++s) {
-      const bool resetting = on && !live && st.reset_left > 0;
-      sub(P, st, live || resetting);
-      if (live) {
-        apply_cart_force(P, st, fx, fy);
-      } else if (resetting) {
-        const int k = (P.settle_steps + P.push_steps) - st.reset_left - P.settle_steps;  // push index
-        if (k >= 0) {
-          T ts, tc;
-          push_force(P, genv, st.episode, (P.theta_mode == BCP_THETA_PER_SUBSTEP) ? k : 0, ts, tc);
-          apply_cart_force(P, st, P.initial_force * tc, P.initial_force * ts);
-        }
-        if (--st.reset_left == 0) { st.done = 0; st.episode += 1; fresh = true; }
-      }
+  return MODE_RESET;
+}
+template <typename T> BCP_HD bool substep_on(int mode, const Env<T>& st) {
+  return mode == MODE_LIVE || (mode == MODE_RESET && st.reset_left > 0);
+}
+// after each p.stepSimulation(): the action force (:201-203) or the reset's push (:329-332)
+template <typename T> BCP_HD void post_substep(const Params<T>& P, Env<T>& st, int64_t genv, int& mode, T fx, T fy) {
+  if (mode == MODE_LIVE) {
+    apply_cart_force(P, st, fx, fy);
+  } else if (mode == MODE_RESET && st.reset_left > 0) {
+    const int k = (P.settle_steps + P.push_steps) - st.reset_left - P.settle_steps;  // push index
+    if (k >= 0) {
+      T ts, tc;
+      push_force(P, genv, st.episode, (P.theta_mode == BCP_THETA_PER_SUBSTEP) ? k : 0, ts, tc);
+      apply_cart_force(P, st, P.initial_force * tc, P.initial_force * ts);
     }
-    if (live && obs) write_obs(st, obs + 14 * r);
+    if (--st.reset_left == 0) { st.done = 0; st.episode += 1; mode = MODE_FRESH; }
   }
-  if (!on) return BCP_REASON_NONE;
-  if (live) {
-    st.steps += 1;
+}
+// steps / done / reward bookkeeping (:239-260); returns the reason code, `live` = reward 1
+template <typename T> BCP_HD int call_end(const Params<T>& P, Env<T>& st, int mode, float* obs, bool& live) {
+  live = mode == MODE_LIVE;
+  if (mode == MODE_LIVE) {
+    st.steps += 1;  // :239
     const int reason = done_reason(P, st);
     if (reason != BCP_REASON_NONE) st.done = 1;
     return reason;
   }
-  if (fresh) {
+  if (mode == MODE_FRESH) {
     if (obs) for (int r = 0; r < P.R; ++r) write_obs(st, obs + 14 * r);
     return BCP_REASON_FRESH;
   }
-  return BCP_REASON_RESETTING;
+  return mode == MODE_RESET ? BCP_REASON_RESETTING : BCP_REASON_NONE;
+}
+
+// The whole call in one go.  `obs` points at this env's dense (R,2,7) block (or nullptr).
+template <typename T, typename STEP>
+BCP_HD int env_call(const Params<T>& P, Env<T>& st, int64_t genv, T fx, T fy, float* obs, const STEP& sub,
+                    bool valid, bool& live) {
+  int mode = call_begin(P, st, valid);
+  for (int r = 0; r < P.R; ++r) {    // :197
+    for (int s = 0; s < P.S; ++s) {  // :198
+      sub(P, st, substep_on(mode, st));  // :199
+      post_substep(P, st, genv, mode, fx, fy);
+    }
+    if (mode == MODE_LIVE && obs) write_obs(st, obs + 14 * r);  // :237
+  }
+  return call_end(P, st, mode, obs, live);
 }
 
 // random-agent action draw (README.md:76-93 protocols), Philox keyed by global env id

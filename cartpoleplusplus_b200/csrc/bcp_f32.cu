@@ -1,7 +1,69 @@
 // FP32 fast mode: FMA contraction allowed (compiled with default -fmad=true).
 #include "bcp_launch_impl.cuh"
+#include "bcp_split.cuh"
 namespace bcp {
 template struct Launch<float>;
+
+size_t split_record_words(const Params<float>& P) { return (size_t)record_words(P); }
+size_t split_counter_words(const Params<float>& P) { return (size_t)(P.R * P.S) * Q_WORDS; }
+
+template <bool FRICTION>
+static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, SplitBuffers b, const SplitIO& io,
+                                   const Stats& st, cudaStream_t s, int* launches, std::vector<cudaEvent_t>* prof) {
+  auto mark = [&]() {
+    if (!prof) return;
+    cudaEvent_t ev;
+    cudaEventCreate(&ev);
+    cudaEventRecord(ev, s);
+    prof->push_back(ev);
+  };
+  const int RS = P.R * P.S, N = P.num_envs;
+  const int rec_words = (int)split_record_words(P);
+  cudaError_t err = cudaMemsetAsync(b.qc, 0, split_counter_words(P) * sizeof(int), s);
+  if (err != cudaSuccess) return err;
+  // k_solve: persistent, as many blocks as stay resident (shared-memory columns bound it)
+  LaunchShape L = shape_for(P, N, false);
+  const int col_stride = P.col_words | 1;  // odd: lane-major columns without bank conflicts
+  L.smem = (size_t)col_stride * L.block * sizeof(float);
+  err = allow_smem(k_solve<float, FRICTION>, L.smem);
+  if (err != cudaSuccess) return err;
+  static int sms = 0, per_sm = 0;
+  static size_t per_sm_smem = (size_t)-1;
+  if (!sms || per_sm_smem != L.smem) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    err = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_solve<float, FRICTION>, L.block, L.smem);
+    if (err != cudaSuccess) return err;
+    if (per_sm < 1) per_sm = 1;
+    per_sm_smem = L.smem;
+  }
+  const int solve_grid = min(sms * per_sm, (N + L.block - 1) / L.block);
+  const int prep_grid = (N + kBlock - 1) / kBlock;
+  mark();
+  for (int k = 0; k <= RS; ++k) {
+    const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
+    int* qc = b.qc + (size_t)(k < RS ? k : 0) * Q_WORDS;
+    k_prep<float, FRICTION><<<prep_grid, kBlock, 0, s>>>(P, f, id, b.recs, rec_words, b.queue, qc, io, st, s_fin, s_set);
+    if (launches) ++*launches;
+    mark();
+    if (k < RS) {
+      k_solve<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, b.queue, qc, col_stride);
+      if (launches) ++*launches;
+      mark();
+    }
+  }
+  return cudaGetLastError();
+}
+cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers b, const void* actions, float* obs,
+                              float* reward, uint8_t* done, uint8_t* reason, StatsPtrs sp, cudaStream_t s, int* launches,
+                              std::vector<cudaEvent_t>* prof) {
+  const Stats st{sp.hist, sp.header, sp.reward_sum};
+  const SplitIO io{actions, obs, reward, done, reason};
+  if (P.any_friction) return step_split_impl<true>(P, f, id, b, io, st, s, launches, prof);
+  return step_split_impl<false>(P, f, id, b, io, st, s, launches, prof);
+}
+
 cudaError_t launch_compact(const uint8_t* flag, int n, int* list, int* count, cudaStream_t s) {
   cudaError_t err = cudaMemsetAsync(count, 0, sizeof(int), s);
   if (err != cudaSuccess) return err;

@@ -71,35 +71,26 @@ __global__ void __launch_bounds__(kBlock) k_step(const __grid_constant__ Params<
   // every lane of the warp goes through the env program (fast path: warp-wide votes); lanes
   // past the end of the shard or with nothing to do carry `on` == false
   const bool valid = e < N;
-  const bool pipelined = P.auto_reset == BCP_AUTO_RESET_PIPELINED;
   Env<T> st;
   st.done = 1;
   st.reset_left = 0;
   if (valid) load_env<T>(f, id, N, e, st);
-  const bool on = valid && (pipelined || !st.done);
-  if (valid && !on) {  // :179-181 - old observation, reward 0, done
-    if (obs && stage_obs) for (int j = 0; j < width; ++j) my[j] = obs[(size_t)e * width + j];
-    if (reward) reward[e] = 0.0f;
-    if (done) done[e] = 1;
-    if (reason) reason[e] = BCP_REASON_NONE;
-  }
+  // an env that does not step keeps its observation (:179-181; pipelined: while it resets)
+  if (valid && st.done && obs && stage_obs) for (int j = 0; j < width; ++j) my[j] = obs[(size_t)e * width + j];
   int a = 0;
   float ax = 0.f, ay = 0.f;
-  if (on) {
+  if (valid) {
     if (P.discrete) a = reinterpret_cast<const int32_t*>(actions)[e];
     else {
       const float2 av = reinterpret_cast<const float2*>(actions)[e];
       ax = av.x; ay = av.y;
     }
-    if (pipelined && st.done && obs && stage_obs) for (int j = 0; j < width; ++j) my[j] = obs[(size_t)e * width + j];
   }
   T fx, fy;
   action_force(P, a, ax, ay, fx, fy);
-  int rs;
-  bool live = on;
-  if (pipelined) rs = env_advance(P, st, P.env_id_offset + e, fx, fy, my, sub, on, live);
-  else rs = env_step(P, st, fx, fy, my, sub, on);
-  if (on) {
+  bool live;
+  const int rs = env_call(P, st, P.env_id_offset + e, fx, fy, my, sub, valid, live);
+  if (valid) {
     store_env<T>(f, id, N, e, st);
     if (reward) reward[e] = live ? 1.0f : 0.0f;
     if (done) done[e] = (uint8_t)st.done;
@@ -204,7 +195,7 @@ __global__ void __launch_bounds__(kBlock) k_rollout(const __grid_constant__ Para
     T fx, fy;
     action_force(P, a, ax, ay, fx, fy);
     bool live;
-    const int rs = env_advance(P, st, genv, fx, fy, o, sub, on, live);
+    const int rs = env_call(P, st, genv, fx, fy, o, sub, on, live);
     if (on) {
       n_sub += (unsigned long long)(P.R * P.S);
       if (live) {

@@ -2,6 +2,7 @@
 // (bcp_f32.cu: fast mode, FMA contraction on; bcp_f64.cu: parity mode, -fmad=false).
 #pragma once
 #include <cuda_runtime.h>
+#include <vector>
 #include "bcp_types.cuh"
 
 namespace bcp {
@@ -25,6 +26,22 @@ template <typename T> struct Launch {
   static cudaError_t export_state(int n, const void* f, const int* id, double* out, cudaStream_t s);
   static cudaError_t import_state(int n, void* f, int* id, const double* in, cudaStream_t s);
 };
+
+// Split pipeline of the fast path (bcp_split.cuh), fp32 only: one call of every env as
+// 2*R*S+1 launches.  `recs` holds num_envs solve records of split_record_words() floats,
+// `queue` num_envs ints, `qc` split_counter_words() ints.
+struct SplitBuffers {
+  float* recs;
+  int* queue;
+  int* qc;
+};
+size_t split_record_words(const Params<float>& P);
+size_t split_counter_words(const Params<float>& P);
+// `prof` (optional): an event is appended before the first kernel and after every kernel, so
+// consecutive events bracket k_prep, k_solve, k_prep, ... of the call.
+cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers b, const void* actions, float* obs,
+                              float* reward, uint8_t* done, uint8_t* reason, StatsPtrs stats, cudaStream_t s,
+                              int* launches, std::vector<cudaEvent_t>* prof);
 
 cudaError_t launch_fma_peak(int use_f64, int iters, double* tflops);
 cudaError_t launch_compact(const uint8_t* flag, int n, int* list, int* count, cudaStream_t s);

@@ -10,8 +10,9 @@
 
 namespace bcp {
 
-enum { NF = BCP_S_MANI + 3 * BCP_MANI_STRIDE, NI = 7 };  // 164 scalars + cnt[3], steps, done, episode, reset_left
-enum { I_CNT = 0, I_STEPS = 3, I_DONE = 4, I_EPISODE = 5, I_RESET_LEFT = 6 };
+enum { NF = BCP_S_MANI + 3 * BCP_MANI_STRIDE, NI = 8 };  // 164 scalars + cnt[3], steps, done, episode, reset_left, mode
+enum { I_CNT = 0, I_STEPS = 3, I_DONE = 4, I_EPISODE = 5, I_RESET_LEFT = 6,
+       I_MODE = 7 };  // MODE_* of the call in flight (split pipeline only; not part of the canonical record)
 
 template <typename T> BCP_HD void load_body(const T* __restrict__ f, size_t N, size_t e, int base, Body<T>& b) {
   for (int i = 0; i < 3; ++i) b.x[i] = f[(size_t)(base + i) * N + e];
@@ -77,7 +78,7 @@ template <typename T> BCP_HD void env_from_canonical(const double* s, Env<T>& st
   for (int i = 0; i < NF; ++i) tmp[i] = (T)s[i];
   int cnt[3];
   for (int m = 0; m < 3; ++m) cnt[m] = (int)s[BCP_S_MANI_CNT + m];
-  const int ids[NI] = {cnt[0], cnt[1], cnt[2], (int)s[BCP_S_STEPS], (int)s[BCP_S_DONE], (int)s[BCP_S_EPISODE], (int)s[BCP_S_RESET_LEFT]};
+  const int ids[NI] = {cnt[0], cnt[1], cnt[2], (int)s[BCP_S_STEPS], (int)s[BCP_S_DONE], (int)s[BCP_S_EPISODE], (int)s[BCP_S_RESET_LEFT], 0};
   load_env<T>(tmp, ids, 1, 0, st);
 }
 template <typename T> BCP_HD void env_to_canonical(const Env<T>& st, double* s) {

@@ -208,6 +208,15 @@ class BatchedBulletCartpole:
     state_dict = get_state
     load_state_dict = set_state
 
+    def profile_begin(self):
+        _lib.check(self._lib.bcp_profile_begin(self._h), self._lib)
+
+    def profile_end(self):
+        """-> dict(ms_prep, ms_solve, n_prep, n_solve): device time per kernel class since profile_begin."""
+        out = (ctypes.c_double * 4)()
+        _lib.check(self._lib.bcp_profile_end(self._h, out), self._lib)
+        return {"ms_prep": out[0], "ms_solve": out[1], "n_prep": int(out[2]), "n_solve": int(out[3])}
+
     @property
     def launch_count(self) -> int:
         return int(self._lib.bcp_launch_count(self._h))

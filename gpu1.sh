@@ -1,8 +1,7 @@
 set -x
 mkdir -p gpurun_out
-python -c "import __graft_entry__ as g; g.smoke()" 2>&1 | tail -4
-timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
-python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/plain3.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k_step -s 3 -c 1 -f -o gpurun_out/prof_r1_v3 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ncu3.log 2>&1
-tail -2 gpurun_out/ncu3.log
-timeout 600 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/bench_a.json 2> gpurun_out/bench_a.err; tail -3 gpurun_out/bench_a.err; cut -c1-900 gpurun_out/bench_a.json
+timeout 900 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
+timeout 600 python scripts/time_split.py 2>&1 | tail -8
+export BCP_SPLIT=1
+python scripts/prof_split.py > gpurun_out/plain3.log 2>&1 && \
+ncu --metrics gpu__time_duration.sum,smsp__thread_inst_executed_per_inst_executed.ratio,smsp__inst_executed.sum,sm__inst_executed.avg.per_cycle_elapsed,sm__warps_active.avg.pct_of_peak_sustained_active --clock-control none -k regex:"k_prep|k_solve" -c 5 --csv --log-file gpurun_out/split_launches.csv python scripts/prof_split.py > gpurun_out/ncu3.log 2>&1

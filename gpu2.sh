@@ -1,8 +1,3 @@
 set -x
 mkdir -p gpurun_out
-timeout 600 python -m pytest tests -m gpu -x -q 2>&1 | tail -5
 timeout 900 python bench.py --steps 20 --warmup 3 > gpurun_out/bench1.json 2> gpurun_out/bench1.err; tail -3 gpurun_out/bench1.err; cat gpurun_out/bench1.json
-timeout 600 python bench.py --steps 10 --warmup 3 --dtype fp64 --no-cpu-baseline > gpurun_out/bench1_f64.json 2>> gpurun_out/bench1.err; cat gpurun_out/bench1_f64.json
-python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -c 60 --csv --log-file gpurun_out/launches_r1.csv python bench.py --steps 4 --warmup 3 --no-cpu-baseline > gpurun_out/ncu.log 2>&1
-tail -3 gpurun_out/ncu.log

@@ -1,5 +1,6 @@
 set -x
 mkdir -p gpurun_out
-python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/plain3.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k_step -s 3 -c 1 -f -o gpurun_out/prof_r1_v2 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/ncu3.log 2>&1
-tail -3 gpurun_out/ncu3.log
+export BCP_SPLIT=1
+python scripts/prof_split.py > gpurun_out/plain3.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:k_solve -s 2 -c 1 -f -o gpurun_out/prof_r1_solve python scripts/prof_split.py > gpurun_out/ncu3.log 2>&1
+tail -2 gpurun_out/ncu3.log

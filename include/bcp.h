@@ -228,6 +228,13 @@ int bcp_bench_fma_peak(int device_ordinal, int use_f64, int iters, double* tflop
 /* number of kernel launches this handle has enqueued (bench's gpu_launches) */
 int64_t bcp_launch_count(const bcp_env* env);
 
+/* Measurement helper (bench.py only): between begin and end every kernel bcp_step launches
+ * is bracketed by CUDA events on the caller's stream.  end() synchronises and writes
+ *   out4 = { ms in k_prep (or the one-launch k_step), ms in k_solve, launches of the
+ *            former, launches of the latter }                                          */
+int bcp_profile_begin(bcp_env* env);
+int bcp_profile_end(bcp_env* env, double* out4);
+
 #ifdef __cplusplus
 }
 #endif

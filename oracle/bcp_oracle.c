@@ -1374,7 +1374,7 @@ int SFX(bcpo_step)(const bcp_config* cfg, double* state, int n_envs, const void*
 
 /* README.md:76-93 random-agent protocol; hist has max_episode_len+1 bins */
 int SFX(bcpo_rollout_random)(const bcp_config* cfg, double* state, int n_envs, int n_steps, uint32_t action_mask,
-                             float* obs, int64_t* hist, int64_t* header, double* reward_sum) {
+                             int max_episodes, float* obs, int64_t* hist, int64_t* header, double* reward_sum) {
   int e;
   const int R_ = cfg->action_repeats;
   const int nb = cfg->max_episode_len + 1;
@@ -1397,6 +1397,8 @@ int SFX(bcpo_rollout_random)(const bcp_config* cfg, double* state, int n_envs, i
         float af[2] = {0, 0}, rew;
         uint8_t dn, rs;
         if (st.done) {
+          /* st.episode counts finished resets: the env has delivered its share of episodes */
+          if (max_episodes > 0 && st.episode >= max_episodes) break;
           env_reset(cfg, &st, cfg->env_id_offset + e, o);
           lrs++;
         }

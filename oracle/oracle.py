@@ -101,9 +101,12 @@ class Oracle:
                              _ptr(reward, ctypes.c_float), _ptr(done, ctypes.c_uint8), _ptr(reason, ctypes.c_uint8))
         return self.obs.copy(), reward, done.astype(bool), reason
 
-    def rollout_random(self, n_steps: int, action_mask: int = 0x1F):
+    def rollout_random(self, n_steps: int, action_mask: int = 0x1F, max_episodes: int = 0):
+        """n_steps env.steps per env with synchronous resets in place (an env stops early once it
+        has finished max_episodes episodes, if > 0)."""
         self._f("bcpo_rollout_random")(ctypes.byref(self.cfg), _ptr(self.state, ctypes.c_double), self.n,
-                                       int(n_steps), ctypes.c_uint32(action_mask), _ptr(self.obs, ctypes.c_float),
+                                       int(n_steps), ctypes.c_uint32(action_mask), int(max_episodes),
+                                       _ptr(self.obs, ctypes.c_float),
                                        _ptr(self.hist, ctypes.c_int64), _ptr(self.header, ctypes.c_int64),
                                        _ptr(self.reward_sum, ctypes.c_double))
 

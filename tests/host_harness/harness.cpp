@@ -4,7 +4,7 @@
 // not reachable from the package and is not a product fallback.
 #include <cstring>
 #include <vector>
-#include "../../cartpoleplusplus_b200/csrc/bcp_fast.cuh"
+#include "../../cartpoleplusplus_b200/csrc/bcp_split.cuh"
 #include "../../cartpoleplusplus_b200/csrc/bcp_state.cuh"
 
 using namespace bcp;
@@ -15,10 +15,14 @@ static int g_fast = 0;
 template <typename T, bool F> struct HostStep {
   mutable std::vector<T> buf;
   int fast;
-  explicit HostStep(const Params<T>& P) : buf((size_t)P.col_words + 1), fast(g_fast) {}
+  mutable std::vector<T> rec;
+  explicit HostStep(const Params<T>& P) : buf((size_t)P.col_words + 1), fast(g_fast), rec((size_t)record_words(P), T(0)) {}
   void operator()(const Params<T>& P, Env<T>& st, bool on) const { if (on) run(P, st, nullptr); }
   void run(const Params<T>& P, Env<T>& st, SubstepInfo* info) const {
-    if (fast) {
+    if (fast == 2) {  // the split pipeline's per-env pieces, composed
+      Col<T> col{buf.data(), 1};
+      substep_split_reference<T, F>(P, st, rec.data(), col, info);
+    } else if (fast) {
       Col<T> col{buf.data(), 1};
       substep_fast<T, F>(P, st, col, true, info);
     } else {
@@ -59,14 +63,9 @@ template <typename T, bool F>
 static void step_all(const Params<T>& P, double* state, int n, const void* actions, float* obs, float* reward,
                      uint8_t* done, uint8_t* reason) {
   const HostStep<T, F> sub(P);
-  const bool pipelined = P.auto_reset == BCP_AUTO_RESET_PIPELINED;
   for (int e = 0; e < n; ++e) {
     Env<T> st;
     env_from_canonical<T>(state + (size_t)e * BCP_STATE_DOUBLES, st);
-    if (st.done && !pipelined) {
-      reward[e] = 0.0f; done[e] = 1; if (reason) reason[e] = 0;
-      continue;
-    }
     int a = 0; float ax = 0, ay = 0;
     if (P.discrete) a = ((const int32_t*)actions)[e];
     else { ax = ((const float*)actions)[2 * e]; ay = ((const float*)actions)[2 * e + 1]; }
@@ -74,7 +73,7 @@ static void step_all(const Params<T>& P, double* state, int n, const void* actio
     action_force(P, a, ax, ay, fx, fy);
     float* o = obs ? obs + (size_t)e * P.R * 14 : nullptr;
     bool live = true;
-    const int rs = pipelined ? env_advance(P, st, P.env_id_offset + e, fx, fy, o, sub, true, live) : env_step(P, st, fx, fy, o, sub, true);
+    const int rs = env_call(P, st, P.env_id_offset + e, fx, fy, o, sub, true, live);
     reward[e] = live ? 1.0f : 0.0f; done[e] = (uint8_t)st.done; if (reason) reason[e] = (uint8_t)rs;
     env_to_canonical<T>(st, state + (size_t)e * BCP_STATE_DOUBLES);
   }

@@ -46,7 +46,7 @@ class HostKernels:
     def __init__(self, cfg, dtype, fast):
         self.cfg = C.copy_config(cfg)
         self.sfx = "_f64" if dtype == "fp64" else "_f32"
-        self.fast = 1 if fast else 0
+        self.fast = int(fast)  # 0 parity path, 1 fast path, 2 split pipeline pieces
         self.n = int(cfg.num_envs)
         self.R = int(cfg.action_repeats)
         self.state = np.zeros((self.n, C.STATE_DOUBLES), dtype=np.float64)
