@@ -1,0 +1,86 @@
+"""The README's random-agent protocols (README.md:76-93) and their summary statistic.
+
+Upstream's `random_action_agent.py --initial-force F --actions "a,b,.." --num-eval N` printed
+one episode length per line for `deciles.py` (deciles.py:4-5:
+`np.percentile(lengths, np.linspace(0, 100, 11))`).  This fork replaced that script by an
+interactive game (random_action_agent.py:876-934), so the protocol is restated here over the
+batched env: episodes are spread over the envs, each env delivers its share, lengths come
+back as the device-side integer histogram and the deciles are reconstructed from it exactly.
+"""
+from __future__ import annotations
+
+import math
+from typing import Iterable, Sequence
+
+import numpy as np
+
+# README.md:77-92 (upstream's numbers, n = 100 each: a sanity window, not a test sample)
+README_DECILES = {
+    (0.0, (0,)): [200] * 11,
+    (0.0, (0, 1, 2, 3, 4)): [16, 22.9, 26, 28, 31.6, 35, 37.4, 42.3, 48.4, 56.1, 79],
+    (55.0, (0,)): [6, 7, 7, 8, 8.6, 9, 11, 12.3, 15, 21, 39],
+    (55.0, (0, 1, 2, 3, 4)): [3, 5.9, 7, 7.7, 8, 9, 10, 11, 13, 15, 32],
+}
+
+
+def lengths_from_histogram(hist: Sequence[int]) -> np.ndarray:
+    """Sorted episode lengths encoded by hist[L] = number of episodes of length L."""
+    hist = np.asarray(hist, dtype=np.int64)
+    return np.repeat(np.arange(hist.size), hist)
+
+
+def deciles_from_histogram(hist: Sequence[int]) -> np.ndarray:
+    """deciles.py:4-5 on the lengths the histogram encodes, without materialising them:
+    np.percentile's linear interpolation between order statistics, exact for integer data."""
+    hist = np.asarray(hist, dtype=np.int64)
+    n = int(hist.sum())
+    if n == 0:
+        raise ValueError("no episodes")
+    cum = np.cumsum(hist)
+    order = lambda k: int(np.searchsorted(cum, k + 1, side="left"))  # noqa: E731  k-th smallest (0-based)
+    out = []
+    for q in np.linspace(0, 100, 11):
+        pos = (n - 1) * q / 100.0
+        lo, hi = int(math.floor(pos)), int(math.ceil(pos))
+        a, b = order(lo), order(hi)
+        out.append(a + (b - a) * (pos - lo))
+    return np.array(out)
+
+
+def ks_two_sample(hist_a: Sequence[int], hist_b: Sequence[int]):
+    """Two-sample Kolmogorov-Smirnov statistic and asymptotic p-value from two histograms over
+    the same integer support (north_star correctness part 3)."""
+    a, b = np.asarray(hist_a, dtype=np.float64), np.asarray(hist_b, dtype=np.float64)
+    na, nb = a.sum(), b.sum()
+    if na == 0 or nb == 0:
+        raise ValueError("empty sample")
+    d = float(np.abs(np.cumsum(a) / na - np.cumsum(b) / nb).max())
+    en = math.sqrt(na * nb / (na + nb))
+    lam = (en + 0.12 + 0.11 / en) * d
+    # Kolmogorov distribution tail (Numerical Recipes probks)
+    p, fac, prev = 0.0, 2.0, 0.0
+    for j in range(1, 101):
+        term = fac * math.exp(-2.0 * lam * lam * j * j)
+        p += term
+        if abs(term) <= 1e-10 * abs(p) or abs(term) <= 1e-3 * prev:
+            break
+        fac, prev = -fac, abs(term)
+    else:
+        p = 1.0
+    return d, float(min(1.0, max(0.0, p)))
+
+
+def run_random_agent(env, num_eval: int, actions: Iterable[int] = (0, 1, 2, 3, 4), calls_per_launch: int = 64,
+                     max_launches: int = 100000):
+    """Run `num_eval` episodes of the random agent on `env` (a BatchedBulletCartpole): each env
+    delivers ceil(num_eval / num_envs) episodes, then idles.  Returns (hist, header dict).
+    Discrete envs draw uniformly from `actions`; continuous envs draw U(-1,1)^2."""
+    per_env = int(math.ceil(num_eval / env.num_envs))
+    env.clear_stats()
+    want = per_env * env.num_envs
+    for _ in range(max_launches):
+        env.rollout_random(calls_per_launch, actions=actions, max_episodes=per_env)
+        hist, header, _ = env.stats()
+        if header["episodes"] >= want:
+            return hist, header
+    raise RuntimeError("random-agent protocol did not finish")
