@@ -123,9 +123,9 @@ typedef struct bcp_config {
   double max_coordinate_velocity; /* 100 */
   double contact_breaking_factor; /* gContactBreakingThreshold 0.02 */
   double max_friction;       /* 10 (combined friction clamp) */
-  double warmstart_factor;   /* 0: contact warm starting off, as btMultiBody
-                                ships (SOLVER_USE_ARTICULATED_WARMSTARTING unset);
-                                >0: cached normal impulse x factor           */
+  double warmstart_factor;   /* cached normal impulse x factor seeds the next solve;
+                                0.85 (btContactSolverInfo default) is what the
+                                README's stability known answer pins; 0 = off   */
   int32_t gyro_term;         /* 1 */
   int32_t reserved1;
 } bcp_config;

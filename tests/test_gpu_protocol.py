@@ -61,14 +61,18 @@ def test_fp32_vs_fp64_episode_lengths_ks(built):
     seeds per mode: the samples must be independent for the test to mean anything."""
     n = 2048
     hists = []
+    # upstream-style switches: with the fork's frictionless cart.urdf the pushes never reach the
+    # pole and every episode times out at 200 - a degenerate sample
+    up = dict(cart_friction=1.0, steps_per_repeat=5, theta_per_reset=True, world_frame_force=True)
     for dtype, seed in (("fp64", 101), ("fp32", 202)):
-        env = _env(n, dtype, seed=seed, initial_force=55.0)
+        env = _env(n, dtype, seed=seed, initial_force=55.0, **up)
         h, hd = protocol.run_random_agent(env, 5 * n)
         assert hd["episodes"] == 5 * n
         hists.append(h)
         env.close()
     d, p = protocol.ks_two_sample(hists[0], hists[1])
     assert p > 0.05, (d, p, protocol.deciles_from_histogram(hists[0]), protocol.deciles_from_histogram(hists[1]))
-    # the README's window for this protocol (upstream models; sanity only): median within a factor of 3
+    # README.md:90-92 for this protocol: median 9 (upstream's models and pybullet, n = 100); the
+    # restated physics gives ~5 - same regime; a sanity window, not a pin
     med = protocol.deciles_from_histogram(hists[1])[5]
-    assert 3 <= med <= 60, med
+    assert 3 <= med <= 27, med

@@ -201,3 +201,23 @@ def test_done_rule_matches_pybullet_euler_formulas():
     assert o.done_reason() == 1
     o.state[0, C.S_POLE] = 3.0  # strict >
     assert o.done_reason() == 2
+
+
+@pytest.mark.parametrize("kw", [dict(), dict(cart_friction=1.0, steps_per_repeat=5)])
+def test_readme_stability_protocol(kw):
+    """README.md:77-80, the reference's one exact known answer: --initial-force=0 --actions="0"
+    => every episode lasts max_episode_len = 200 steps.  This pins the contact warm start
+    (config.PhysicsParams.warmstart_factor): without it the pole falls after ~49 steps."""
+    from cartpoleplusplus_b200 import protocol
+    cfg = make_config(default_opts(initial_force=0.0, **kw), True, num_envs=8, dtype="fp64", seed=7)
+    ora = Oracle(cfg, dtype="fp64")
+    ora.state[:, C.S_DONE] = 1
+    ora.rollout_random(450, action_mask=0x1, max_episodes=2)
+    assert ora.hist[200] == 16 and ora.hist.sum() == 16
+    assert np.array_equal(protocol.deciles_from_histogram(ora.hist), [200] * 11)
+    off = C.PhysicsParams(warmstart_factor=0.0)
+    cfg0 = make_config(default_opts(initial_force=0.0, **kw), True, num_envs=2, dtype="fp64", seed=7, physics=off)
+    ora0 = Oracle(cfg0, dtype="fp64")
+    ora0.state[:, C.S_DONE] = 1
+    ora0.rollout_random(210, action_mask=0x1, max_episodes=1)
+    assert ora0.hist[200] == 0  # the parameter matters: this is what the known answer rules out
