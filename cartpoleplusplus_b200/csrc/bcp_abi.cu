@@ -129,6 +129,8 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
   {
     const char* sv = getenv("BCP_SPLIT");
     h->use_split = (!h->f64()) && (sv ? atoi(sv) != 0 : cfg->num_envs >= 4096);
+    // the pooled solver implements the default row order and the two-direction friction cone
+    if (cfg->manifold_order != 0 || cfg->friction_dirs != 2 || !cfg->cone_friction) h->use_split = 0;
     if (h->use_split) {
       A((void**)&h->split.recs, bcp::split_record_words(h->p32) * N * sizeof(float));
       A((void**)&h->split.queue, N * sizeof(int));

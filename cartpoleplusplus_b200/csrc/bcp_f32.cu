@@ -23,7 +23,9 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   if (err != cudaSuccess) return err;
   // k_solve: persistent, as many blocks as stay resident (shared-memory columns bound it)
   LaunchShape L = shape_for(P, N, false);
-  const int col_stride = P.col_words | 1;  // odd: lane-major columns without bank conflicts
+  // lane-major columns of float4: stride / 4 odd => conflict-free 16-byte accesses
+  const int col4 = (solve_layout(P).words >> 2) | 1;
+  const int col_stride = col4 * 4;
   L.smem = (size_t)col_stride * L.block * sizeof(float);
   err = allow_smem(k_solve<float, FRICTION>, L.smem);
   if (err != cudaSuccess) return err;

@@ -103,6 +103,7 @@ BCP_HD T row_rhs(const Params<T>& P, T rel_vel, T distance_in, T comb_rest, T in
   if (is_friction) positionalError = 0;
   else if (distance > 0) velocityError -= distance / P.dt;
   else positionalError = -distance * P.erp2 / P.dt;
+  if (invD < T(0.0)) return positionalError + velocityError;  // velocity units (bcp_solve.cuh rows)
   return positionalError * invD + velocityError * invD;
 }
 

@@ -1,0 +1,330 @@
+// bcp_solve.cuh — the pooled solver's row format and its branch-free iteration.
+//
+// Rows of the split pipeline (bcp_split.cuh) are stored for 16-byte accesses, in "velocity
+// units" so that nothing but the applied impulse changes during a solve:
+//   one-body row  (8 words) : j[3] d[3] rhsV invD            rhsV = rhs / invD
+//   two-body row (12 words) : ja[3] jb[3] n[3] rhsV invD pad
+// and   deltaImpulse = (rhsV - applied*cfm - J.dv) * invD,
+//       residual     =  rhsV - applied*cfm - J.dv            (= deltaImpulse / jacDiagABInv)
+// unless the impulse is clamped (then deltaImpulse_clamped / invD).  Applied impulses live
+// in registers (every slot index below is a compile-time constant).  Contact slots a lane
+// does not use are ZERO rows: they solve to a zero impulse with a zero residual, so the
+// iteration has no per-lane branch at all - only warp-uniform trip counts (the largest
+// contact count per manifold among the warp's envs).  Same row order, limits, cone clip and
+// early exit as bcp_fast.cuh / the oracle.
+#pragma once
+#include "bcp_fast.cuh"
+
+namespace bcp {
+
+enum { SW1 = 8, SW2 = 12 };  // words per one-body / two-body row
+enum { S1_J = 0, S1_D = 3, S1_RHSV = 6, S1_INVD = 7 };
+enum { S2_JA = 0, S2_JB = 3, S2_N = 6, S2_RHSV = 9, S2_INVD = 10 };
+enum { SLOT_GC = 0, SLOT_CP = 4, SLOT_GP = 8, N_SLOTS = 12 };  // applied-impulse slots: pair * 4 + contact
+
+// word offsets of the three pairs' row blocks inside a column / a record's row area
+struct SolveLayout {
+  int base[3], rpc[3], words;
+};
+template <typename T> BCP_HD SolveLayout solve_layout(const Params<T>& P) {
+  SolveLayout L;
+  int at = 0;
+  for (int m = 0; m < 3; ++m) {
+    L.base[m] = at;
+    L.rpc[m] = P.rows_per_contact[m];
+    at += 4 * L.rpc[m] * (m == BCP_PAIR_CART_POLE ? (int)SW2 : (int)SW1);
+  }
+  L.words = at;
+  return L;
+}
+
+template <typename T> BCP_HD void ld4(const T* p, T o[4]) {
+  o[0] = p[0]; o[1] = p[1]; o[2] = p[2]; o[3] = p[3];
+}
+#if defined(__CUDA_ARCH__)
+template <> __device__ __forceinline__ void ld4<float>(const float* p, float o[4]) {
+  const float4 v = *reinterpret_cast<const float4*>(p);
+  o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+}
+#endif
+// reciprocal / reciprocal square root for the residual and the cone scale: one MUFU each on
+// the device (2 ulp; neither feeds a clamp decision), exact on the host and in double
+BCP_HD float fast_rcp(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return 1.0f / x;
+#endif
+}
+BCP_HD double fast_rcp(double x) { return 1.0 / x; }
+BCP_HD float fast_rsqrt(float x) {
+#if defined(__CUDA_ARCH__)
+  float r;
+  asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+  return r;
+#else
+  return 1.0f / sqrtf(x);
+#endif
+}
+BCP_HD double fast_rsqrt(double x) { return 1.0 / sqrt(x); }
+BCP_HD float bmin(float a, float b) { return fminf(a, b); }
+BCP_HD float bmax(float a, float b) { return fmaxf(a, b); }
+BCP_HD double bmin(double a, double b) { return fmin(a, b); }
+BCP_HD double bmax(double a, double b) { return fmax(a, b); }
+
+// solver-side body: deltas only, plus the constants M^-1 is made of
+template <typename T> struct SBodyLite {
+  T dwl[3], dv[3], invI[3], invM;
+};
+// everything a lane carries through a solve
+template <typename T> struct SolveRegs {
+  SBodyLite<T> cart, pole;
+  T apn[N_SLOTS];     // applied normal impulses
+  T apf[N_SLOTS][2];  // applied friction impulses
+};
+
+// clamp the accumulated impulse; returns the residual of the row
+template <typename T> BCP_HD T clamp_row(T& ap, T& delta, T u, T invD, T lo, T hi) {
+  const T sum = ap + delta;
+  const T nv = bmin(bmax(sum, lo), hi);
+  delta = nv - ap;
+  ap = nv;
+  return (nv != sum) ? delta * fast_rcp(invD) : u;
+}
+
+template <typename T> BCP_HD T solve_row1(const Params<T>& P, const T* row, SBodyLite<T>& B, T& ap, T lo, T hi, T cfm) {
+  T a[4], b[4];
+  ld4(row, a);
+  ld4(row + 4, b);  // a = j0 j1 j2 d0 | b = d1 d2 rhsV invD
+  const T jdv = (a[0] * B.dwl[0] + a[1] * B.dwl[1] + a[2] * B.dwl[2]) + (a[3] * B.dv[0] + b[0] * B.dv[1] + b[1] * B.dv[2]);
+  const T u = b[2] - ap * cfm - jdv;
+  T delta = u * b[3];
+  const T res = clamp_row(ap, delta, u, b[3], lo, hi);
+  const T lm = B.invM * delta;
+  B.dwl[0] += a[0] * (B.invI[0] * delta); B.dwl[1] += a[1] * (B.invI[1] * delta); B.dwl[2] += a[2] * (B.invI[2] * delta);
+  B.dv[0] += a[3] * lm; B.dv[1] += b[0] * lm; B.dv[2] += b[1] * lm;
+  return res;
+}
+template <typename T>
+BCP_HD T solve_row2(const Params<T>& P, const T* row, SBodyLite<T>& A, SBodyLite<T>& B, T& ap, T lo, T hi, T cfm) {
+  T a[4], b[4], c[4];
+  ld4(row, a);
+  ld4(row + 4, b);
+  ld4(row + 8, c);  // a = ja0 ja1 ja2 jb0 | b = jb1 jb2 n0 n1 | c = n2 rhsV invD -
+  const T jdv = (a[0] * A.dwl[0] + a[1] * A.dwl[1] + a[2] * A.dwl[2]) + (a[3] * B.dwl[0] + b[0] * B.dwl[1] + b[1] * B.dwl[2]) +
+                (b[2] * (A.dv[0] - B.dv[0]) + b[3] * (A.dv[1] - B.dv[1]) + c[0] * (A.dv[2] - B.dv[2]));
+  const T u = c[1] - ap * cfm - jdv;
+  T delta = u * c[2];
+  const T res = clamp_row(ap, delta, u, c[2], lo, hi);
+  const T la = A.invM * delta, lb = B.invM * delta;
+  A.dwl[0] += a[0] * (A.invI[0] * delta); A.dwl[1] += a[1] * (A.invI[1] * delta); A.dwl[2] += a[2] * (A.invI[2] * delta);
+  B.dwl[0] += a[3] * (B.invI[0] * delta); B.dwl[1] += b[0] * (B.invI[1] * delta); B.dwl[2] += b[1] * (B.invI[2] * delta);
+  A.dv[0] += b[2] * la; A.dv[1] += b[3] * la; A.dv[2] += c[0] * la;
+  B.dv[0] -= b[2] * lb; B.dv[1] -= b[3] * lb; B.dv[2] -= c[0] * lb;
+  return res;
+}
+
+// cone clip of the two friction impulses of one contact (resolveConeFrictionConstraintRows)
+template <typename T>
+BCP_HD T cone_clip(T& apA, T& apB, T& dA, T& dB, T uA, T uB, T invDA, T invDB, T L) {
+  // Bullet clips (sumA, sumB) to the circle of radius |L| through the angle (sin, cos) =
+  // (sumA, sumB) / r; outside the circle both clamps bind, i.e. the pair is scaled by |L| / r
+  const T sumA = apA + dA, sumB = apB + dB;
+  const T ss = sumA * sumA + sumB * sumB;
+  const bool clip = ss >= L * L && ss > T(0.0);
+  const T sc = clip ? babs(L) * fast_rsqrt(ss) : T(1.0);
+  const T nA = sumA * sc, nB = sumB * sc;
+  dA = nA - apA;
+  dB = nB - apB;
+  apA = nA;
+  apB = nB;
+  const T rA = clip ? dA * fast_rcp(invDA) : uA;
+  const T rB = clip ? dB * fast_rcp(invDB) : uB;
+  return rA + rB;
+}
+template <typename T> BCP_HD T solve_cone1(const Params<T>& P, const T* rowA, SBodyLite<T>& B, T& apA, T& apB, T L, T cfm) {
+  const T* rowB = rowA + SW1;
+  T a[4], b[4], c[4], d[4];
+  ld4(rowA, a); ld4(rowA + 4, b); ld4(rowB, c); ld4(rowB + 4, d);
+  const T jdvB = (c[0] * B.dwl[0] + c[1] * B.dwl[1] + c[2] * B.dwl[2]) + (c[3] * B.dv[0] + d[0] * B.dv[1] + d[1] * B.dv[2]);
+  const T jdvA = (a[0] * B.dwl[0] + a[1] * B.dwl[1] + a[2] * B.dwl[2]) + (a[3] * B.dv[0] + b[0] * B.dv[1] + b[1] * B.dv[2]);
+  const T uB = d[2] - apB * cfm - jdvB, uA = b[2] - apA * cfm - jdvA;
+  T dB = uB * d[3], dA = uA * b[3];
+  const T res = cone_clip(apA, apB, dA, dB, uA, uB, b[3], d[3], L);
+  const T lA = B.invM * dA, lB = B.invM * dB;
+  B.dwl[0] += a[0] * (B.invI[0] * dA); B.dwl[1] += a[1] * (B.invI[1] * dA); B.dwl[2] += a[2] * (B.invI[2] * dA);
+  B.dv[0] += a[3] * lA; B.dv[1] += b[0] * lA; B.dv[2] += b[1] * lA;
+  B.dwl[0] += c[0] * (B.invI[0] * dB); B.dwl[1] += c[1] * (B.invI[1] * dB); B.dwl[2] += c[2] * (B.invI[2] * dB);
+  B.dv[0] += c[3] * lB; B.dv[1] += d[0] * lB; B.dv[2] += d[1] * lB;
+  return res;
+}
+template <typename T>
+BCP_HD T solve_cone2(const Params<T>& P, const T* rowA, SBodyLite<T>& A, SBodyLite<T>& B, T& apA, T& apB, T L, T cfm) {
+  const T* rowB = rowA + SW2;
+  T a[4], b[4], c[4], e[4], f[4], g[4];
+  ld4(rowA, a); ld4(rowA + 4, b); ld4(rowA + 8, c); ld4(rowB, e); ld4(rowB + 4, f); ld4(rowB + 8, g);
+  const T dl[3] = {A.dv[0] - B.dv[0], A.dv[1] - B.dv[1], A.dv[2] - B.dv[2]};
+  const T jdvB = (e[0] * A.dwl[0] + e[1] * A.dwl[1] + e[2] * A.dwl[2]) + (e[3] * B.dwl[0] + f[0] * B.dwl[1] + f[1] * B.dwl[2]) +
+                 (f[2] * dl[0] + f[3] * dl[1] + g[0] * dl[2]);
+  const T jdvA = (a[0] * A.dwl[0] + a[1] * A.dwl[1] + a[2] * A.dwl[2]) + (a[3] * B.dwl[0] + b[0] * B.dwl[1] + b[1] * B.dwl[2]) +
+                 (b[2] * dl[0] + b[3] * dl[1] + c[0] * dl[2]);
+  const T uB = g[1] - apB * cfm - jdvB, uA = c[1] - apA * cfm - jdvA;
+  T dB = uB * g[2], dA = uA * c[2];
+  const T res = cone_clip(apA, apB, dA, dB, uA, uB, c[2], g[2], L);
+  {
+    const T la = A.invM * dA, lb = B.invM * dA;
+    A.dwl[0] += a[0] * (A.invI[0] * dA); A.dwl[1] += a[1] * (A.invI[1] * dA); A.dwl[2] += a[2] * (A.invI[2] * dA);
+    B.dwl[0] += a[3] * (B.invI[0] * dA); B.dwl[1] += b[0] * (B.invI[1] * dA); B.dwl[2] += b[1] * (B.invI[2] * dA);
+    A.dv[0] += b[2] * la; A.dv[1] += b[3] * la; A.dv[2] += c[0] * la;
+    B.dv[0] -= b[2] * lb; B.dv[1] -= b[3] * lb; B.dv[2] -= c[0] * lb;
+  }
+  {
+    const T la = A.invM * dB, lb = B.invM * dB;
+    A.dwl[0] += e[0] * (A.invI[0] * dB); A.dwl[1] += e[1] * (A.invI[1] * dB); A.dwl[2] += e[2] * (A.invI[2] * dB);
+    B.dwl[0] += e[3] * (B.invI[0] * dB); B.dwl[1] += f[0] * (B.invI[1] * dB); B.dwl[2] += f[1] * (B.invI[2] * dB);
+    A.dv[0] += f[2] * la; A.dv[1] += f[3] * la; A.dv[2] += g[0] * la;
+    B.dv[0] -= f[2] * lb; B.dv[1] -= f[3] * lb; B.dv[2] -= g[0] * lb;
+  }
+  return res;
+}
+
+// One projected Gauss-Seidel iteration over a lane's column: ground-pole, cart-pole,
+// ground-cart normal rows, then their friction rows (manifold_order 0).  mx[m] = slots to
+// sweep per pair (warp-uniform; a lane's unused slots are zero rows).  Returns the largest
+// squared residual.
+template <typename T, bool FRICTION>
+BCP_HD T solve_iteration(const Params<T>& P, const T* colp, const SolveLayout& L, const int mx[3], SolveRegs<T>& R) {
+  T lsr = 0;
+  const T cfm_n = P.cfm_normal, cfm_f = P.cfm_friction, big = T(1e10f);
+#define BCP_ACC(r_) { const T r__ = (r_); const T r2__ = r__ * r__; lsr = (lsr > r2__) ? lsr : r2__; }
+  {
+    const int st = L.rpc[BCP_PAIR_GROUND_POLE] * SW1;
+    const T* row = colp + L.base[BCP_PAIR_GROUND_POLE];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
+      BCP_ACC(solve_row1(P, row + j * st, R.pole, R.apn[SLOT_GP + j], T(0.0), big, cfm_n));
+    }
+  }
+  {
+    const int st = L.rpc[BCP_PAIR_CART_POLE] * SW2;
+    const T* row = colp + L.base[BCP_PAIR_CART_POLE];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (j >= mx[BCP_PAIR_CART_POLE]) break;
+      BCP_ACC(solve_row2(P, row + j * st, R.cart, R.pole, R.apn[SLOT_CP + j], T(0.0), big, cfm_n));
+    }
+  }
+  {
+    const int st = L.rpc[BCP_PAIR_GROUND_CART] * SW1;
+    const T* row = colp + L.base[BCP_PAIR_GROUND_CART];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      if (j >= mx[BCP_PAIR_GROUND_CART]) break;
+      BCP_ACC(solve_row1(P, row + j * st, R.cart, R.apn[SLOT_GC + j], T(0.0), big, cfm_n));
+    }
+  }
+  if (FRICTION) {
+    if (L.rpc[BCP_PAIR_GROUND_POLE] == 3) {
+      const T* row = colp + L.base[BCP_PAIR_GROUND_POLE] + SW1;
+      const T mu = P.mu[BCP_PAIR_GROUND_POLE];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
+        BCP_ACC(solve_cone1(P, row + j * 3 * SW1, R.pole, R.apf[SLOT_GP + j][0], R.apf[SLOT_GP + j][1], mu * R.apn[SLOT_GP + j], cfm_f));
+      }
+    }
+    if (L.rpc[BCP_PAIR_CART_POLE] == 3) {
+      const T* row = colp + L.base[BCP_PAIR_CART_POLE] + SW2;
+      const T mu = P.mu[BCP_PAIR_CART_POLE];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (j >= mx[BCP_PAIR_CART_POLE]) break;
+        BCP_ACC(solve_cone2(P, row + j * 3 * SW2, R.cart, R.pole, R.apf[SLOT_CP + j][0], R.apf[SLOT_CP + j][1], mu * R.apn[SLOT_CP + j], cfm_f));
+      }
+    }
+    if (L.rpc[BCP_PAIR_GROUND_CART] == 3) {
+      const T* row = colp + L.base[BCP_PAIR_GROUND_CART] + SW1;
+      const T mu = P.mu[BCP_PAIR_GROUND_CART];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        if (j >= mx[BCP_PAIR_GROUND_CART]) break;
+        BCP_ACC(solve_cone1(P, row + j * 3 * SW1, R.cart, R.apf[SLOT_GC + j][0], R.apf[SLOT_GC + j][1], mu * R.apn[SLOT_GC + j], cfm_f));
+      }
+    }
+  }
+#undef BCP_ACC
+  return lsr;
+}
+
+// ---- writing rows in this format (k_prep) ----
+// one-body row (A = static ground, B = body): J = [R^T (rB x -axis), -axis]
+template <typename T>
+BCP_HD T put_row1(const Params<T>& P, T* row, FBody<T>& B, const T pb[3], const T axis[3], T dist, T rest,
+                  bool is_friction, T warm_impulse) {
+  T j[3], d[3];
+  local_jac(B, pb, axis, T(-1.0), j);
+  for (int i = 0; i < 3; ++i) d[i] = -axis[i];
+  const T cfm = is_friction ? P.cfm_friction : P.cfm_normal;
+  const T den = ang_denom(B, j) + B.invM * dot3(d, d) + cfm;
+  const T invD = (den > Lim<T>::eps()) ? T(1.0) / den : T(0.0);
+  const T rel_vel = dot3(j, B.wl) + dot3(d, B.v);
+  for (int i = 0; i < 3; ++i) { row[S1_J + i] = j[i]; row[S1_D + i] = d[i]; }
+  row[S1_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
+  row[S1_INVD] = invD;
+  if (warm_impulse != T(0.0)) {
+    for (int i = 0; i < 3; ++i) { B.dwl[i] += j[i] * B.invI[i] * warm_impulse; B.dv[i] += d[i] * (B.invM * warm_impulse); }
+  }
+  return warm_impulse;
+}
+template <typename T>
+BCP_HD T put_row2(const Params<T>& P, T* row, FBody<T>& A, FBody<T>& B, const T pa[3], const T pb[3], const T axis[3],
+                  T dist, T rest, bool is_friction, T warm_impulse) {
+  T ja[3], jb[3];
+  local_jac(A, pa, axis, T(1.0), ja);
+  local_jac(B, pb, axis, T(-1.0), jb);
+  const T cfm = is_friction ? P.cfm_friction : P.cfm_normal;
+  const T nn = dot3(axis, axis);
+  const T den = (ang_denom(A, ja) + A.invM * nn) + (ang_denom(B, jb) + B.invM * nn) + cfm;
+  const T invD = (den > Lim<T>::eps()) ? T(1.0) / den : T(0.0);
+  const T rel_vel = (dot3(ja, A.wl) + dot3(axis, A.v)) + (dot3(jb, B.wl) - dot3(axis, B.v));
+  for (int i = 0; i < 3; ++i) { row[S2_JA + i] = ja[i]; row[S2_JB + i] = jb[i]; row[S2_N + i] = axis[i]; }
+  row[S2_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
+  row[S2_INVD] = invD;
+  row[11] = 0;
+  if (warm_impulse != T(0.0)) {
+    for (int i = 0; i < 3; ++i) {
+      A.dwl[i] += ja[i] * A.invI[i] * warm_impulse; A.dv[i] += axis[i] * (A.invM * warm_impulse);
+      B.dwl[i] += jb[i] * B.invI[i] * warm_impulse; B.dv[i] -= axis[i] * (B.invM * warm_impulse);
+    }
+  }
+  return warm_impulse;
+}
+// rows of manifold m (normal row, then the friction rows along btPlaneSpace1(normal)) and the
+// warm-start impulses of its normal rows into apn[4]
+template <typename T, bool FRICTION, bool TWO>
+BCP_HD void put_rows(const Params<T>& P, T* rows, T* apn, int m, int rpc, const Manifold<T>& mf, const WorldPt<T>* wp,
+                     FBody<T>& A, FBody<T>& B) {
+  const int W = TWO ? (int)SW2 : (int)SW1;
+  const T rest = P.rest[m];
+  for (int j = 0; j < mf.count; ++j) {
+    T* row = rows + j * rpc * W;
+    const T warm = (P.warmstart > T(0.0)) ? mf.p[j].imp * P.warmstart : T(0.0);
+    if (TWO) apn[j] = put_row2(P, row, A, B, wp[j].pa, wp[j].pb, mf.p[j].n, mf.p[j].dist, rest, false, warm);
+    else apn[j] = put_row1(P, row, B, wp[j].pb, mf.p[j].n, mf.p[j].dist, rest, false, warm);
+    if (FRICTION && rpc > 1) {
+      T d1[3], d2[3];
+      plane_space(mf.p[j].n, d1, d2);
+      if (TWO) put_row2(P, row + W, A, B, wp[j].pa, wp[j].pb, d1, T(0), rest, true, T(0));
+      else put_row1(P, row + W, B, wp[j].pb, d1, T(0), rest, true, T(0));
+      if (rpc > 2) {
+        if (TWO) put_row2(P, row + 2 * W, A, B, wp[j].pa, wp[j].pb, d2, T(0), rest, true, T(0));
+        else put_row1(P, row + 2 * W, B, wp[j].pb, d2, T(0), rest, true, T(0));
+      }
+    }
+  }
+}
+
+}  // namespace bcp

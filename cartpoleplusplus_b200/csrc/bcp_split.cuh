@@ -9,38 +9,26 @@
 //   k_prep  one env per lane, SoA state, coalesced: finishes the previous substep
 //           (velocities += deltas, integrate, force application / reset progress, pose capture)
 //           and sets up the next (forward dynamics, narrowphase, manifold caches, contact rows).
-//           Rows go to a per-env SOLVE RECORD in global memory (L2-resident) and the env is
-//           queued, predicted-long solves first.
+//           Rows go to a per-env SOLVE RECORD in global memory (L2-resident; row format of
+//           bcp_solve.cuh) and the env is queued, predicted-long solves first.
 //   k_solve persistent warps; every lane pulls envs off the queue, copies the record's live
 //           rows into its shared-memory column and iterates; a lane whose env has converged
 //           retires it and pulls the next, so all 32 lanes sweep on every iteration.
-// The arithmetic of an env is exactly substep_fast's (same functions, same order).
+// Collision, manifolds, forward dynamics and integration are substep_fast's functions; the
+// rows are the same rows in the solver's 16-byte format (bcp_solve.cuh).
 #pragma once
 #include <cstring>
-#include "bcp_fast.cuh"
+#include "bcp_solve.cuh"
 #include "bcp_state.cuh"
 
 namespace bcp {
 
 // ---- solve record (global memory, one per env, 16-byte aligned) ----
-// words 0..15: header; then the three pairs' rows, padded to 12 / 16 words per row
-enum { REC_C_GC = 0, REC_C_CP = 1, REC_C_GP = 2, REC_ITERS = 3, REC_DVEL = 4, REC_HEADER = 16 };
-enum { RW1_PAD = 12, RW2_PAD = 16 };
+// words 0..15 header, 16..27 applied normal impulses per slot (warm start in, result out),
+// 28..31 pad, then the row area in the layout of solve_layout()
+enum { REC_C_GC = 0, REC_C_CP = 1, REC_C_GP = 2, REC_ITERS = 3, REC_DVEL = 4, REC_APN = 16, REC_ROWS = 32 };
 
-template <typename T> BCP_HD RowLayout record_layout(const Params<T>& P) {
-  RowLayout L;
-  int at = REC_HEADER;
-  for (int m = 0; m < 3; ++m) {
-    L.base[m] = at;
-    L.w[m] = (m == BCP_PAIR_CART_POLE) ? (int)RW2_PAD : (int)RW1_PAD;
-    at += 4 * P.rows_per_contact[m] * L.w[m];
-  }
-  return L;
-}
-template <typename T> BCP_HD int record_words(const Params<T>& P) {
-  const RowLayout L = record_layout(P);
-  return L.base[2] + 4 * P.rows_per_contact[2] * L.w[2];
-}
+template <typename T> BCP_HD int record_words(const Params<T>& P) { return REC_ROWS + solve_layout(P).words; }
 BCP_HD int as_int(float x) {
 #if defined(__CUDA_ARCH__)
   return __float_as_int(x);
@@ -57,20 +45,48 @@ BCP_HD float as_real(int i, float) {
 }
 BCP_HD int as_int(double x) { return (int)x; }
 BCP_HD double as_real(int i, double) { return (double)i; }
+BCP_HD int slot_of_pair(int m) { return m == BCP_PAIR_GROUND_CART ? (int)SLOT_GC : (m == BCP_PAIR_CART_POLE ? (int)SLOT_CP : (int)SLOT_GP); }
 
 // setup half of a substep for one env: rows + header into `rec`, the unconstrained
 // velocities parked in the state (angular in the BODY frame until split_finish).
 template <typename T, bool FRICTION>
 BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
+  Posed<T> gbox, cbox, pbox;
   FBody<T> cart, pole;
-  const Col<T> col{rec, 1};
-  const RowLayout L = record_layout(P);
-  fast_setup<T, FRICTION>(P, st, col, L, cart, pole, on, nullptr);
+  const SolveLayout L = solve_layout(P);
+  BCP_WARP_SYNC();
+  if (on) {
+    for (int i = 0; i < 3; ++i) { gbox.x[i] = P.ground.x0[i]; gbox.h[i] = P.ground.h[i]; }
+    for (int i = 0; i < 9; ++i) gbox.R[i] = (i % 4 == 0) ? T(1.0) : T(0.0);
+    pose_box(st.cart, P.cart, cbox);
+    pose_box(st.pole, P.pole, pbox);
+    const T zero3[3] = {0, 0, 0};
+    fbody_begin(P, st.cart, P.cart, cbox.R, st.pend_f, st.pend_t, cart);
+    fbody_begin(P, st.pole, P.pole, pbox.R, zero3, zero3, pole);
+  }
+  for (int m = 0; m < 3; ++m) {
+    BCP_WARP_SYNC();
+    if (on) {
+      const Posed<T>& A = (m == BCP_PAIR_CART_POLE) ? cbox : gbox;
+      const Posed<T>& B = (m == BCP_PAIR_GROUND_CART) ? cbox : pbox;
+      Contact<T> cs[4];
+      WorldPt<T> wp[4];
+      const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, cs);
+      for (int k = 0; k < nc; ++k) manifold_add(st.mani[m], A, B, cs[k], P.breaking[m]);
+      manifold_refresh(st.mani[m], A, B, P.breaking[m], wp);
+      T* rows = rec + REC_ROWS + L.base[m];
+      T* apn = rec + REC_APN + slot_of_pair(m);
+      if (m == BCP_PAIR_GROUND_CART) put_rows<T, FRICTION, false>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, cart, cart);
+      else if (m == BCP_PAIR_CART_POLE) put_rows<T, FRICTION, true>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, cart, pole);
+      else put_rows<T, FRICTION, false>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, pole, pole);
+    }
+  }
+  BCP_WARP_SYNC();
   if (on) {
     rec[REC_C_GC] = as_real(st.mani[BCP_PAIR_GROUND_CART].count, T(0));
     rec[REC_C_CP] = as_real(st.mani[BCP_PAIR_CART_POLE].count, T(0));
     rec[REC_C_GP] = as_real(st.mani[BCP_PAIR_GROUND_POLE].count, T(0));
-    for (int i = 0; i < 3; ++i) {  // warm-start deltas (zero unless warmstart_factor > 0)
+    for (int i = 0; i < 3; ++i) {  // warm-start deltas
       rec[REC_DVEL + i] = cart.dwl[i]; rec[REC_DVEL + 3 + i] = cart.dv[i];
       rec[REC_DVEL + 6 + i] = pole.dwl[i]; rec[REC_DVEL + 9 + i] = pole.dv[i];
       st.cart.w[i] = cart.wl[i]; st.cart.v[i] = cart.v[i];
@@ -80,81 +96,71 @@ BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
   }
 }
 
-// record -> compact shared-memory column (live rows only); returns the contact counts
-template <typename T>
-BCP_HD void record_to_column(const Params<T>& P, const T* rec, const Col<T>& col, int cnt[3]) {
-  const RowLayout R = record_layout(P), C = compact_layout(P);
+// what a lane needs to start a solve: contact counts, warm-start deltas and impulses
+template <typename T> BCP_HD void solve_begin(const Params<T>& P, const T* rec, int cnt[3], SolveRegs<T>& R) {
   cnt[0] = as_int(rec[REC_C_GC]); cnt[1] = as_int(rec[REC_C_CP]); cnt[2] = as_int(rec[REC_C_GP]);
-  for (int m = 0; m < 3; ++m) {
-    const int rows = cnt[m] * P.rows_per_contact[m];
-    for (int r = 0; r < rows; ++r) {
-      const T* src = rec + R.base[m] + r * R.w[m];
-      const int dst = C.base[m] + r * C.w[m];
-      for (int w = 0; w < C.w[m]; ++w) col[dst + w] = src[w];
-    }
+  for (int i = 0; i < 3; ++i) {
+    R.cart.dwl[i] = rec[REC_DVEL + i]; R.cart.dv[i] = rec[REC_DVEL + 3 + i];
+    R.pole.dwl[i] = rec[REC_DVEL + 6 + i]; R.pole.dv[i] = rec[REC_DVEL + 9 + i];
+    R.cart.invI[i] = T(1.0) / P.cart.I[i];
+    R.pole.invI[i] = T(1.0) / P.pole.I[i];
+  }
+  R.cart.invM = P.cart.inv_mass;
+  R.pole.invM = P.pole.inv_mass;
+#pragma unroll
+  for (int s = 0; s < N_SLOTS; ++s) {
+    const int m = s >> 2, j = s & 3;  // SLOT_* = pair * 4
+    R.apn[s] = (j < cnt[m]) ? rec[REC_APN + s] : T(0.0);
+    R.apf[s][0] = 0;
+    R.apf[s][1] = 0;
   }
 }
 // solve results -> record: iteration count, velocity deltas, applied normal impulses
-template <typename T>
-BCP_HD void column_to_record(const Params<T>& P, T* rec, const Col<T>& col, const int cnt[3], int iters,
-                             const FBody<T>& cart, const FBody<T>& pole) {
-  const RowLayout R = record_layout(P), C = compact_layout(P);
+template <typename T> BCP_HD void solve_end(T* rec, const int cnt[3], int iters, const SolveRegs<T>& R) {
   rec[REC_ITERS] = as_real(iters, T(0));
   for (int i = 0; i < 3; ++i) {
-    rec[REC_DVEL + i] = cart.dwl[i]; rec[REC_DVEL + 3 + i] = cart.dv[i];
-    rec[REC_DVEL + 6 + i] = pole.dwl[i]; rec[REC_DVEL + 9 + i] = pole.dv[i];
+    rec[REC_DVEL + i] = R.cart.dwl[i]; rec[REC_DVEL + 3 + i] = R.cart.dv[i];
+    rec[REC_DVEL + 6 + i] = R.pole.dwl[i]; rec[REC_DVEL + 9 + i] = R.pole.dv[i];
   }
-  for (int m = 0; m < 3; ++m) {
-    const int ap = (m == BCP_PAIR_CART_POLE) ? (int)R2_APPL : (int)R1_APPL;
-    const int rpc = P.rows_per_contact[m];
-    for (int j = 0; j < cnt[m]; ++j) rec[R.base[m] + j * rpc * R.w[m] + ap] = col[C.base[m] + j * rpc * C.w[m] + ap];
-  }
-}
-template <typename T> BCP_HD void solver_bodies(const Params<T>& P, const T* rec, FBody<T>& cart, FBody<T>& pole) {
-  for (int i = 0; i < 3; ++i) {
-    cart.dwl[i] = rec[REC_DVEL + i]; cart.dv[i] = rec[REC_DVEL + 3 + i];
-    pole.dwl[i] = rec[REC_DVEL + 6 + i]; pole.dv[i] = rec[REC_DVEL + 9 + i];
-    cart.invI[i] = T(1.0) / P.cart.I[i];
-    pole.invI[i] = T(1.0) / P.pole.I[i];
-  }
-  cart.invM = P.cart.inv_mass;
-  pole.invM = P.pole.inv_mass;
+#pragma unroll
+  for (int s = 0; s < N_SLOTS; ++s)
+    if ((s & 3) < cnt[s >> 2]) rec[REC_APN + s] = R.apn[s];
 }
 
 // finish half of a substep: velocities += deltas, integrate, impulses -> manifold cache
 template <typename T> BCP_HD void split_finish(const Params<T>& P, Env<T>& st, const T* rec) {
   FBody<T> cart, pole;
-  solver_bodies(P, rec, cart, pole);
-  quat_to_mat(st.cart.q, cart.R);
-  quat_to_mat(st.pole.q, pole.R);
   for (int i = 0; i < 3; ++i) {
+    cart.dwl[i] = rec[REC_DVEL + i]; cart.dv[i] = rec[REC_DVEL + 3 + i];
+    pole.dwl[i] = rec[REC_DVEL + 6 + i]; pole.dv[i] = rec[REC_DVEL + 9 + i];
     cart.wl[i] = st.cart.w[i]; cart.v[i] = st.cart.v[i];
     pole.wl[i] = st.pole.w[i]; pole.v[i] = st.pole.v[i];
   }
-  const RowLayout R = record_layout(P);
-  for (int m = 0; m < 3; ++m) {
-    const int ap = (m == BCP_PAIR_CART_POLE) ? (int)R2_APPL : (int)R1_APPL;
-    for (int j = 0; j < st.mani[m].count; ++j) st.mani[m].p[j].imp = rec[R.base[m] + j * P.rows_per_contact[m] * R.w[m] + ap];
-  }
+  quat_to_mat(st.cart.q, cart.R);
+  quat_to_mat(st.pole.q, pole.R);
+  for (int m = 0; m < 3; ++m)
+    for (int j = 0; j < st.mani[m].count; ++j) st.mani[m].p[j].imp = rec[REC_APN + slot_of_pair(m) + j];
   fbody_finish(P, cart, st.cart);
   fbody_finish(P, pole, st.pole);
 }
 
-// host-side composition (tests): the whole substep through a record, one env
+// host-side composition (tests): the whole substep through a record, one env.  Slots the env
+// does not use must be zero rows, as in k_solve's columns.
 template <typename T, bool FRICTION>
-BCP_HD void substep_split_reference(const Params<T>& P, Env<T>& st, T* rec, const Col<T>& col, SubstepInfo* info) {
+BCP_HD void substep_split_reference(const Params<T>& P, Env<T>& st, T* rec, SubstepInfo* info) {
+  const SolveLayout L = solve_layout(P);
+  for (int i = 0; i < L.words; ++i) rec[REC_ROWS + i] = 0;
   split_setup<T, FRICTION>(P, st, rec, true);
   int cnt[3];
-  record_to_column(P, rec, col, cnt);
-  FBody<T> cart, pole;
-  solver_bodies(P, rec, cart, pole);
+  SolveRegs<T> R;
+  solve_begin(P, rec, cnt, R);
   int it = 0;
   for (int k = 0; k < P.solver_iterations; ++k) {
-    const T lsr = fast_iteration<T, FRICTION>(P, col, cnt[0], cnt[1], cnt[2], cart, pole);
+    const T lsr = solve_iteration<T, FRICTION>(P, rec + REC_ROWS, L, cnt, R);
     it = k + 1;
     if (lsr <= P.residual_thr || k >= P.solver_iterations - 1) break;
   }
-  column_to_record(P, rec, col, cnt, it, cart, pole);
+  solve_end(rec, cnt, it, R);
   split_finish(P, st, rec);
   if (info) {
     info->iterations = it;
@@ -258,11 +264,11 @@ __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Para
 }
 
 // persistent pooled solve: every lane keeps pulling envs until the queue is dry.
-// Shared memory: one column per lane, lane-major with an odd stride ([lane][col_stride]), so
-// that both access patterns are conflict-free - 32 lanes reading the same word of their own
-// columns (the sweep) and 32 lanes writing consecutive words of ONE column (the cooperative
-// copy of a record's rows when a lane takes a new env).
-constexpr int kFetchMin = 6;  // idle lanes that trigger a retire + fetch round
+// Shared memory: one column per lane, lane-major ([lane][col_stride] words, col_stride / 4 odd):
+// conflict-free both for 32 lanes reading the same float4 of their own columns (the sweep) and
+// for 32 lanes writing consecutive float4 of ONE column (the cooperative copy of a record's
+// rows when a lane takes a new env).
+constexpr int kFetchMin = 6;  // idle lanes that trigger a fetch round
 
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
@@ -270,29 +276,21 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
   const unsigned FULL = 0xffffffffu;
   T* const smem = reinterpret_cast<T*>(bcp_smem);
   const int lane = threadIdx.x & 31, warp_base = threadIdx.x - lane;
-  Col<T> col;
-  col.base = smem + (size_t)threadIdx.x * col_stride;
-  col.stride = 1;
-  const RowLayout RL = record_layout(P), CL = compact_layout(P);
+  const T* const colp = smem + (size_t)threadIdx.x * col_stride;
+  const SolveLayout L = solve_layout(P);
   const int N = P.num_envs;
   const int n_long = qc[Q_LONG], total = n_long + qc[Q_SHORT];
   const unsigned lt = (1u << lane) - 1;
   int w_next = 0, w_end = 0;  // the warp's slice of the queue (uniform)
   bool exhausted = total == 0;
-  FBody<T> cart, pole;
-  int cnt[3] = {0, 0, 0};
+  SolveRegs<T> R;
+  int cnt[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
   int it = 0;
   T* rec = nullptr;
   bool busy = false;
   while (true) {
     const unsigned idle = __ballot_sync(FULL, !busy);
-    const bool any_busy = idle != FULL;
-    if (idle && (!any_busy || (!exhausted && __popc(idle) >= kFetchMin))) {
-      if (!busy && rec) {  // retire: iteration count, velocity deltas, applied normal impulses
-        column_to_record(P, rec, col, cnt, it, cart, pole);
-        rec = nullptr;
-        cnt[0] = cnt[1] = cnt[2] = 0;
-      }
+    if (idle && (idle == FULL || (!exhausted && __popc(idle) >= kFetchMin))) {
       unsigned need = idle;
       int idx = -1;
       while (need && !exhausted) {
@@ -315,36 +313,45 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
         const int pos = idx < n_long ? idx : N - 1 - (idx - n_long);
         env = queue[pos];
         rec = recs + (size_t)env * rec_words;
-        cnt[0] = as_int(rec[REC_C_GC]); cnt[1] = as_int(rec[REC_C_CP]); cnt[2] = as_int(rec[REC_C_GP]);
-        solver_bodies(P, rec, cart, pole);
+        solve_begin(P, rec, cnt, R);
         it = 0;
         busy = true;
       }
-      // the warp copies the live rows of every newly taken env into its lane's column
+      // the warp copies the rows of every newly taken env into its lane's column, zero rows
+      // in the contact slots the env does not use
       unsigned taken = __ballot_sync(FULL, idx >= 0);
       while (taken) {
         const int src = __ffs(taken) - 1;
         taken &= taken - 1;
         const int e_src = __shfl_sync(FULL, env, src);
-        const T* r_src = recs + (size_t)e_src * rec_words;
-        T* c_dst = smem + (size_t)(warp_base + src) * col_stride;
+        const float4* r_src = reinterpret_cast<const float4*>(recs + (size_t)e_src * rec_words + REC_ROWS);
+        float4* c_dst = reinterpret_cast<float4*>(smem + (size_t)(warp_base + src) * col_stride);
 #pragma unroll
         for (int m = 0; m < 3; ++m) {
-          const int wc = CL.w[m], wp = RL.w[m];
-          const int nw = __shfl_sync(FULL, cnt[m], src) * P.rows_per_contact[m] * wc;
-          for (int i = lane; i < nw; i += 32) {
-            const int r = i / wc, w = i - r * wc;
-            c_dst[CL.base[m] + i] = r_src[RL.base[m] + r * wp + w];
-          }
+          const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
+          const int live4 = (__shfl_sync(FULL, cnt[m], src) * L.rpc[m] * w) >> 2, all4 = (4 * L.rpc[m] * w) >> 2;
+          const int b4 = L.base[m] >> 2;
+          for (int i = lane; i < all4; i += 32) c_dst[b4 + i] = (i < live4) ? r_src[b4 + i] : make_float4(0.f, 0.f, 0.f, 0.f);
         }
       }
       __syncwarp();
+#pragma unroll
+      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
     }
     if (!__any_sync(FULL, busy)) break;
-    const T lsr = fast_iteration<T, FRICTION>(P, col, busy ? cnt[0] : 0, busy ? cnt[1] : 0, busy ? cnt[2] : 0, cart, pole);
+    const T lsr = solve_iteration<T, FRICTION>(P, colp, L, mx, R);
+    bool conv = false;
     if (busy) {
       it++;
-      if (lsr <= P.residual_thr || it >= P.solver_iterations) busy = false;
+      conv = lsr <= P.residual_thr || it >= P.solver_iterations;
+    }
+    if (__any_sync(FULL, conv)) {
+      if (conv) {  // retire at once: the lane keeps sweeping its stale column until it is refilled
+        solve_end(rec, cnt, it, R);
+        busy = false;
+      }
+#pragma unroll
+      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
     }
   }
 }

@@ -20,8 +20,7 @@ template <typename T, bool F> struct HostStep {
   void operator()(const Params<T>& P, Env<T>& st, bool on) const { if (on) run(P, st, nullptr); }
   void run(const Params<T>& P, Env<T>& st, SubstepInfo* info) const {
     if (fast == 2) {  // the split pipeline's per-env pieces, composed
-      Col<T> col{buf.data(), 1};
-      substep_split_reference<T, F>(P, st, rec.data(), col, info);
+      substep_split_reference<T, F>(P, st, rec.data(), info);
     } else if (fast) {
       Col<T> col{buf.data(), 1};
       substep_fast<T, F>(P, st, col, true, info);
