@@ -36,15 +36,15 @@ struct bcp_env {
   bcp_config cfg;
   bcp::Params<float> p32;
   bcp::Params<double> p64;
-  void* fdata = nullptr;  // SoA float fields, [NF][N] in the handle's scalar type
-  int* idata = nullptr;   // SoA int fields, [NI][N]
+  void* fdata = nullptr;  // env records, [N][NF] in the handle's scalar type (bcp_state.cuh)
+  int* idata = nullptr;   // [N][NI]
   unsigned long long* hist = nullptr;
   unsigned long long* header = nullptr;
   double* reward_sum = nullptr;
   int* list = nullptr;   // compacted env indices for masked resets
   int* count = nullptr;
   double* staging = nullptr;  // canonical records for get/set_state
-  bcp::SplitBuffers split = {nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
+  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1};  // solve records / queue of the split pipeline
   int use_split = 0;
   bool profiling = false;
   std::vector<cudaEvent_t> prof_events;  // bracketing every kernel of bcp_step while profiling
@@ -121,8 +121,9 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
   A((void**)&h->list, N * sizeof(int));
   A((void**)&h->count, sizeof(int));
   if (err == cudaSuccess) {  // no state until reset (bullet_cartpole.py:147-148): every env starts "done"
-    std::vector<int> ones(N, 1);
-    err = cudaMemcpy(h->idata + (size_t)bcp::I_DONE * N, ones.data(), N * sizeof(int), cudaMemcpyHostToDevice);
+    std::vector<int> init(N * bcp::NI, 0);
+    for (size_t e = 0; e < N; ++e) init[e * bcp::NI + bcp::I_DONE] = 1;
+    err = cudaMemcpy(h->idata, init.data(), init.size() * sizeof(int), cudaMemcpyHostToDevice);
   }
   // fp32 with enough envs to fill the machine: env.step runs as the split pipeline
   // (BCP_SPLIT=0/1 overrides; the one-launch fast kernel is the alternative)
@@ -135,6 +136,10 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
       A((void**)&h->split.recs, bcp::split_record_words(h->p32) * N * sizeof(float));
       A((void**)&h->split.queue, N * sizeof(int));
       A((void**)&h->split.qc, bcp::split_counter_words(h->p32) * sizeof(int));
+      for (int k = 0; k < 2; ++k) {
+        A((void**)&h->split.bins[k], bcp::split_bins_words(h->p32) * sizeof(int));
+        A((void**)&h->split.cnts[k], 8 * sizeof(int));
+      }
     }
   }
   if (err != cudaSuccess) {
@@ -151,6 +156,7 @@ int bcp_destroy(bcp_env* h) {
   cudaFree(h->fdata); cudaFree(h->idata); cudaFree(h->hist); cudaFree(h->header);
   cudaFree(h->reward_sum); cudaFree(h->list); cudaFree(h->count); cudaFree(h->staging);
   cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc);
+  for (int k = 0; k < 2; ++k) { cudaFree(h->split.bins[k]); cudaFree(h->split.cnts[k]); }
   delete h;
   return 0;
 }

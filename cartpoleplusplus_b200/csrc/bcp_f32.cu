@@ -6,9 +6,10 @@ template struct Launch<float>;
 
 size_t split_record_words(const Params<float>& P) { return (size_t)record_words(P); }
 size_t split_counter_words(const Params<float>& P) { return (size_t)(P.R * P.S) * Q_WORDS; }
+size_t split_bins_words(const Params<float>& P) { return (size_t)N_BINS * (size_t)P.num_envs; }
 
 template <bool FRICTION>
-static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, SplitBuffers b, const SplitIO& io,
+static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, SplitBuffers& b, const SplitIO& io,
                                    const Stats& st, cudaStream_t s, int* launches, std::vector<cudaEvent_t>* prof) {
   auto mark = [&]() {
     if (!prof) return;
@@ -21,6 +22,14 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   const int rec_words = (int)split_record_words(P);
   cudaError_t err = cudaMemsetAsync(b.qc, 0, split_counter_words(P) * sizeof(int), s);
   if (err != cudaSuccess) return err;
+  const int nxt = b.cur < 0 ? 0 : 1 - b.cur;
+  err = cudaMemsetAsync(b.cnts[nxt], 0, N_BINS * sizeof(int), s);
+  if (err != cudaSuccess) return err;
+  VisitOrder vo;
+  vo.bins = b.cur < 0 ? nullptr : b.bins[b.cur];
+  vo.cnt = b.cur < 0 ? nullptr : b.cnts[b.cur];
+  vo.next_bins = b.bins[nxt];
+  vo.next_cnt = b.cnts[nxt];
   // k_solve: persistent, as many blocks as stay resident (shared-memory columns bound it)
   LaunchShape L = shape_for(P, N, false);
   // lane-major columns of float4: stride / 4 odd => conflict-free 16-byte accesses
@@ -46,7 +55,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   for (int k = 0; k <= RS; ++k) {
     const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
     int* qc = b.qc + (size_t)(k < RS ? k : 0) * Q_WORDS;
-    k_prep<float, FRICTION><<<prep_grid, kBlock, 0, s>>>(P, f, id, b.recs, rec_words, b.queue, qc, io, st, s_fin, s_set);
+    k_prep<float, FRICTION><<<prep_grid, kBlock, 0, s>>>(P, f, id, b.recs, rec_words, b.queue, qc, io, st, vo, s_fin, s_set);
     if (launches) ++*launches;
     mark();
     if (k < RS) {
@@ -55,9 +64,10 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
       mark();
     }
   }
+  b.cur = nxt;
   return cudaGetLastError();
 }
-cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers b, const void* actions, float* obs,
+cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers& b, const void* actions, float* obs,
                               float* reward, uint8_t* done, uint8_t* reason, StatsPtrs sp, cudaStream_t s, int* launches,
                               std::vector<cudaEvent_t>* prof) {
   const Stats st{sp.hist, sp.header, sp.reward_sum};

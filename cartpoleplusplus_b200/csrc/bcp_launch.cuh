@@ -34,12 +34,16 @@ struct SplitBuffers {
   float* recs;
   int* queue;
   int* qc;
+  int* bins[2];  // visiting order, double buffered: [8][num_envs] env ids each
+  int* cnts[2];  // [8] each
+  int cur;       // which of the two the next call reads; -1: no order yet (identity)
 };
+size_t split_bins_words(const Params<float>& P);
 size_t split_record_words(const Params<float>& P);
 size_t split_counter_words(const Params<float>& P);
 // `prof` (optional): an event is appended before the first kernel and after every kernel, so
 // consecutive events bracket k_prep, k_solve, k_prep, ... of the call.
-cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers b, const void* actions, float* obs,
+cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers& b, const void* actions, float* obs,
                               float* reward, uint8_t* done, uint8_t* reason, StatsPtrs stats, cudaStream_t s,
                               int* launches, std::vector<cudaEvent_t>* prof);
 

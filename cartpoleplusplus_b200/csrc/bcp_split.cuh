@@ -184,15 +184,40 @@ struct SplitIO {
   uint8_t* reason;
 };
 
+// Visiting order of the envs.  The kernel that closes a call files every env under its contact
+// regime (which of the three pairs hold points: 8 bins); the next call's k_prep launches walk
+// the bins, so that the 32 envs of a warp - and the 32 queue entries a solver warp takes - run
+// the same narrowphase branches and need the same row slots.  cnt == nullptr: identity order.
+enum { N_BINS = 8 };
+struct VisitOrder {
+  const int* bins;  // [N_BINS][N] env ids
+  const int* cnt;   // [N_BINS]
+  int* next_bins;   // filled by the closing kernel
+  int* next_cnt;
+};
+__device__ __forceinline__ int visit(const VisitOrder& vo, int i, int N) {
+  if (!vo.cnt) return i < N ? i : -1;
+  int at = i;
+#pragma unroll
+  for (int b = 0; b < N_BINS; ++b) {
+    const int c = vo.cnt[b];
+    if (at < c) return vo.bins[(size_t)b * N + at];
+    at -= c;
+  }
+  return -1;
+}
+
 // s_fin: substep to finish (-1: none, this is the first kernel of the call)
 // s_set: substep to set up  (-1: none, this is the last kernel of the call)
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int* __restrict__ queue,
-                                                 int* __restrict__ qc_set, SplitIO io, Stats stats, int s_fin, int s_set) {
+                                                 int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
+                                                 int s_set) {
   const int N = P.num_envs;
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  const bool valid = e < N;
+  const int e_visit = visit(vo, blockIdx.x * blockDim.x + threadIdx.x, N);
+  const bool valid = e_visit >= 0;
+  const int e = valid ? e_visit : 0;
   const int64_t genv = P.env_id_offset + e;
   const int width = 14 * P.R;
   T* rec = recs + (size_t)(valid ? e : 0) * rec_words;
@@ -203,7 +228,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Para
   int mode = MODE_IDLE;
   if (valid) {
     load_env<T>(f, id, N, e, st);
-    mode = id[(size_t)I_MODE * N + e];
+    mode = id[(size_t)e * NI + I_MODE];
   }
   if (s_fin < 0) mode = call_begin(P, st, valid);
   if (s_fin >= 0 && valid) {
@@ -256,10 +281,24 @@ __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Para
       const unsigned w = __popc(__ballot_sync(0xffffffffu, live));
       if ((threadIdx.x & 31) == 0 && w) atomicAdd(&stats.header[1], (unsigned long long)w);
     }
+    if (vo.next_cnt) {  // file the env under the contact regime its next call will run in
+      int key = (st.mani[BCP_PAIR_GROUND_POLE].count > 0 ? 4 : 0) | (st.mani[BCP_PAIR_CART_POLE].count > 0 ? 2 : 0) |
+                (st.mani[BCP_PAIR_GROUND_CART].count > 0 ? 1 : 0);
+      if (st.done && st.reset_left == 0 && P.auto_reset == BCP_AUTO_RESET_PIPELINED) key = 3;  // teleported onto the cart
+      const unsigned act = __ballot_sync(0xffffffffu, valid);
+      if (valid) {
+        const unsigned peers = __match_any_sync(act, key);
+        const int lane = threadIdx.x & 31, leader = __ffs(peers) - 1;
+        int base = 0;
+        if (lane == leader) base = atomicAdd(&vo.next_cnt[key], __popc(peers));
+        base = __shfl_sync(peers, base, leader);
+        vo.next_bins[(size_t)key * N + base + __popc(peers & ((1u << lane) - 1))] = e;
+      }
+    }
   }
   if (valid) {
     store_env<T>(f, id, N, e, st);
-    id[(size_t)I_MODE * N + e] = mode;
+    id[(size_t)e * NI + I_MODE] = mode;
   }
 }
 

@@ -1,10 +1,13 @@
-// bcp_state.cuh — structure-of-arrays env state in HBM and its register image.
+// bcp_state.cuh — env state in HBM and its register image.
 //
-// Layout: `fdata[f * N + e]` for the NF float fields (f follows the canonical record
-// of include/bcp.h: bodies, pending force/torque, 3 x 4 manifold points) and
-// `idata[f * N + e]` for the NI integer fields.  Consecutive lanes of a warp own
-// consecutive envs, so every field access is one fully coalesced 128/256-byte
-// transaction; manifold points beyond the live count are neither read nor written.
+// Layout: one RECORD per env, `fdata[e * NF + f]` for the NF float fields (f follows the
+// canonical record of include/bcp.h: bodies, pending force/torque, 3 x 4 manifold points)
+// and `idata[e * NI + f]` for the NI integer fields.  Records are 16-byte aligned and are
+// moved with 16-byte accesses (float4 / double2): a lane reads its env's 128-byte body
+// block and only the manifold blocks that hold points.  Record-per-env (rather than
+// field-major arrays) is what lets the split pipeline visit envs in ANY order - it regroups
+// them every step so that a warp's 32 envs are in the same contact regime - without
+// scattering every access over 32 sectors.
 #pragma once
 #include "bcp_types.cuh"
 
@@ -14,76 +17,131 @@ enum { NF = BCP_S_MANI + 3 * BCP_MANI_STRIDE, NI = 8 };  // 164 scalars + cnt[3]
 enum { I_CNT = 0, I_STEPS = 3, I_DONE = 4, I_EPISODE = 5, I_RESET_LEFT = 6,
        I_MODE = 7 };  // MODE_* of the call in flight (split pipeline only; not part of the canonical record)
 
-template <typename T> BCP_HD void load_body(const T* __restrict__ f, size_t N, size_t e, int base, Body<T>& b) {
-  for (int i = 0; i < 3; ++i) b.x[i] = f[(size_t)(base + i) * N + e];
-  for (int i = 0; i < 4; ++i) b.q[i] = f[(size_t)(base + 3 + i) * N + e];
-  for (int i = 0; i < 3; ++i) b.v[i] = f[(size_t)(base + 7 + i) * N + e];
-  for (int i = 0; i < 3; ++i) b.w[i] = f[(size_t)(base + 10 + i) * N + e];
+// 16-byte copies between a record and a local array; n is a multiple of 16 / sizeof(T)
+template <typename T> BCP_HD void copy16(const T* __restrict__ src, T* __restrict__ dst, int n) {
+  for (int i = 0; i < n; ++i) dst[i] = src[i];
 }
-template <typename T> BCP_HD void store_body(T* __restrict__ f, size_t N, size_t e, int base, const Body<T>& b) {
-  for (int i = 0; i < 3; ++i) f[(size_t)(base + i) * N + e] = b.x[i];
-  for (int i = 0; i < 4; ++i) f[(size_t)(base + 3 + i) * N + e] = b.q[i];
-  for (int i = 0; i < 3; ++i) f[(size_t)(base + 7 + i) * N + e] = b.v[i];
-  for (int i = 0; i < 3; ++i) f[(size_t)(base + 10 + i) * N + e] = b.w[i];
+#if defined(__CUDA_ARCH__)
+template <> __device__ __forceinline__ void copy16<float>(const float* __restrict__ src, float* __restrict__ dst, int n) {
+#pragma unroll
+  for (int i = 0; i < n; i += 4) {
+    const float4 v = *reinterpret_cast<const float4*>(src + i);
+    dst[i] = v.x; dst[i + 1] = v.y; dst[i + 2] = v.z; dst[i + 3] = v.w;
+  }
+}
+template <> __device__ __forceinline__ void copy16<double>(const double* __restrict__ src, double* __restrict__ dst, int n) {
+#pragma unroll
+  for (int i = 0; i < n; i += 2) {
+    const double2 v = *reinterpret_cast<const double2*>(src + i);
+    dst[i] = v.x; dst[i + 1] = v.y;
+  }
+}
+#endif
+template <typename T> BCP_HD void store16(T* __restrict__ dst, const T* __restrict__ src, int n) {
+  for (int i = 0; i < n; ++i) dst[i] = src[i];
+}
+#if defined(__CUDA_ARCH__)
+template <> __device__ __forceinline__ void store16<float>(float* __restrict__ dst, const float* __restrict__ src, int n) {
+#pragma unroll
+  for (int i = 0; i < n; i += 4) *reinterpret_cast<float4*>(dst + i) = make_float4(src[i], src[i + 1], src[i + 2], src[i + 3]);
+}
+template <> __device__ __forceinline__ void store16<double>(double* __restrict__ dst, const double* __restrict__ src, int n) {
+#pragma unroll
+  for (int i = 0; i < n; i += 2) *reinterpret_cast<double2*>(dst + i) = make_double2(src[i], src[i + 1]);
+}
+#endif
+
+template <typename T> BCP_HD void unpack_body(const T* b, Body<T>& o) {
+  for (int i = 0; i < 3; ++i) { o.x[i] = b[i]; o.v[i] = b[7 + i]; o.w[i] = b[10 + i]; }
+  for (int i = 0; i < 4; ++i) o.q[i] = b[3 + i];
+}
+template <typename T> BCP_HD void pack_body(const Body<T>& o, T* b) {
+  for (int i = 0; i < 3; ++i) { b[i] = o.x[i]; b[7 + i] = o.v[i]; b[10 + i] = o.w[i]; }
+  for (int i = 0; i < 4; ++i) b[3 + i] = o.q[i];
 }
 
+// `N` is unused (kept so that call sites read the same for any layout)
 template <typename T>
 BCP_HD void load_env(const T* __restrict__ f, const int* __restrict__ id, size_t N, size_t e, Env<T>& st) {
-  load_body(f, N, e, BCP_S_CART, st.cart);
-  load_body(f, N, e, BCP_S_POLE, st.pole);
-  for (int i = 0; i < 3; ++i) { st.pend_f[i] = f[(size_t)(BCP_S_PEND_F + i) * N + e]; st.pend_t[i] = f[(size_t)(BCP_S_PEND_T + i) * N + e]; }
+  (void)N;
+  const T* r = f + e * NF;
+  const int* ir = id + e * NI;
+  int iv[NI];
+#if defined(__CUDA_ARCH__)
+  {
+    const int4 a = *reinterpret_cast<const int4*>(ir), b = *reinterpret_cast<const int4*>(ir + 4);
+    iv[0] = a.x; iv[1] = a.y; iv[2] = a.z; iv[3] = a.w; iv[4] = b.x; iv[5] = b.y; iv[6] = b.z; iv[7] = b.w;
+  }
+#else
+  for (int i = 0; i < NI; ++i) iv[i] = ir[i];
+#endif
+  T head[BCP_S_MANI];
+  copy16(r, head, BCP_S_MANI);
+  unpack_body(head + BCP_S_CART, st.cart);
+  unpack_body(head + BCP_S_POLE, st.pole);
+  for (int i = 0; i < 3; ++i) { st.pend_f[i] = head[BCP_S_PEND_F + i]; st.pend_t[i] = head[BCP_S_PEND_T + i]; }
   for (int m = 0; m < 3; ++m) {
-    st.mani[m].count = id[(size_t)(I_CNT + m) * N + e];
-    for (int k = 0; k < 4; ++k) {
-      if (k < st.mani[m].count) {
-        const int base = BCP_S_MANI + m * BCP_MANI_STRIDE + k * BCP_MANI_POINT;
-        MPoint<T>& p = st.mani[m].p[k];
-        for (int i = 0; i < 3; ++i) { p.la[i] = f[(size_t)(base + i) * N + e]; p.lb[i] = f[(size_t)(base + 3 + i) * N + e]; p.n[i] = f[(size_t)(base + 6 + i) * N + e]; }
-        p.dist = f[(size_t)(base + 9) * N + e];
-        p.imp = f[(size_t)(base + 10) * N + e];
+    st.mani[m].count = iv[I_CNT + m];
+    if (st.mani[m].count > 0) {
+      T blk[BCP_MANI_STRIDE];
+      copy16(r + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
+      for (int k = 0; k < 4; ++k) {
+        if (k < st.mani[m].count) {
+          const T* q = blk + k * BCP_MANI_POINT;
+          MPoint<T>& p = st.mani[m].p[k];
+          for (int i = 0; i < 3; ++i) { p.la[i] = q[i]; p.lb[i] = q[3 + i]; p.n[i] = q[6 + i]; }
+          p.dist = q[9];
+          p.imp = q[10];
+        }
       }
     }
   }
-  st.steps = id[(size_t)I_STEPS * N + e];
-  st.done = id[(size_t)I_DONE * N + e];
-  st.episode = id[(size_t)I_EPISODE * N + e];
-  st.reset_left = id[(size_t)I_RESET_LEFT * N + e];
+  st.steps = iv[I_STEPS];
+  st.done = iv[I_DONE];
+  st.episode = iv[I_EPISODE];
+  st.reset_left = iv[I_RESET_LEFT];
 }
 template <typename T>
 BCP_HD void store_env(T* __restrict__ f, int* __restrict__ id, size_t N, size_t e, const Env<T>& st) {
-  store_body(f, N, e, BCP_S_CART, st.cart);
-  store_body(f, N, e, BCP_S_POLE, st.pole);
-  for (int i = 0; i < 3; ++i) { f[(size_t)(BCP_S_PEND_F + i) * N + e] = st.pend_f[i]; f[(size_t)(BCP_S_PEND_T + i) * N + e] = st.pend_t[i]; }
+  (void)N;
+  T* r = f + e * NF;
+  int* ir = id + e * NI;
+  T head[BCP_S_MANI];
+  pack_body(st.cart, head + BCP_S_CART);
+  pack_body(st.pole, head + BCP_S_POLE);
+  for (int i = 0; i < 3; ++i) { head[BCP_S_PEND_F + i] = st.pend_f[i]; head[BCP_S_PEND_T + i] = st.pend_t[i]; }
+  store16(r, head, BCP_S_MANI);
   for (int m = 0; m < 3; ++m) {
-    id[(size_t)(I_CNT + m) * N + e] = st.mani[m].count;
-    for (int k = 0; k < 4; ++k) {
-      if (k < st.mani[m].count) {
-        const int base = BCP_S_MANI + m * BCP_MANI_STRIDE + k * BCP_MANI_POINT;
+    if (st.mani[m].count > 0) {
+      T blk[BCP_MANI_STRIDE];
+      for (int k = 0; k < 4; ++k) {
+        T* q = blk + k * BCP_MANI_POINT;
         const MPoint<T>& p = st.mani[m].p[k];
-        for (int i = 0; i < 3; ++i) { f[(size_t)(base + i) * N + e] = p.la[i]; f[(size_t)(base + 3 + i) * N + e] = p.lb[i]; f[(size_t)(base + 6 + i) * N + e] = p.n[i]; }
-        f[(size_t)(base + 9) * N + e] = p.dist;
-        f[(size_t)(base + 10) * N + e] = p.imp;
+        const bool live = k < st.mani[m].count;
+        for (int i = 0; i < 3; ++i) { q[i] = live ? p.la[i] : T(0); q[3 + i] = live ? p.lb[i] : T(0); q[6 + i] = live ? p.n[i] : T(0); }
+        q[9] = live ? p.dist : T(0);
+        q[10] = live ? p.imp : T(0);
       }
+      store16(r + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
     }
   }
-  id[(size_t)I_STEPS * N + e] = st.steps;
-  id[(size_t)I_DONE * N + e] = st.done;
-  id[(size_t)I_EPISODE * N + e] = st.episode;
-  id[(size_t)I_RESET_LEFT * N + e] = st.reset_left;
+  // the mode word (I_MODE) belongs to the split pipeline and is written by it
+  ir[I_CNT] = st.mani[0].count; ir[I_CNT + 1] = st.mani[1].count; ir[I_CNT + 2] = st.mani[2].count;
+  ir[I_STEPS] = st.steps; ir[I_DONE] = st.done; ir[I_EPISODE] = st.episode; ir[I_RESET_LEFT] = st.reset_left;
 }
 
 // canonical record (doubles, include/bcp.h) <-> register image
 template <typename T> BCP_HD void env_from_canonical(const double* s, Env<T>& st) {
-  T tmp[NF];
+  alignas(16) T tmp[NF];
   for (int i = 0; i < NF; ++i) tmp[i] = (T)s[i];
   int cnt[3];
   for (int m = 0; m < 3; ++m) cnt[m] = (int)s[BCP_S_MANI_CNT + m];
-  const int ids[NI] = {cnt[0], cnt[1], cnt[2], (int)s[BCP_S_STEPS], (int)s[BCP_S_DONE], (int)s[BCP_S_EPISODE], (int)s[BCP_S_RESET_LEFT], 0};
+  alignas(16) const int ids[NI] = {cnt[0], cnt[1], cnt[2], (int)s[BCP_S_STEPS], (int)s[BCP_S_DONE], (int)s[BCP_S_EPISODE], (int)s[BCP_S_RESET_LEFT], 0};
   load_env<T>(tmp, ids, 1, 0, st);
 }
 template <typename T> BCP_HD void env_to_canonical(const Env<T>& st, double* s) {
-  T tmp[NF];
-  int ids[NI];
+  alignas(16) T tmp[NF];
+  alignas(16) int ids[NI];
   for (int i = 0; i < NF; ++i) tmp[i] = 0;
   store_env<T>(tmp, ids, 1, 0, st);
   for (int i = 0; i < NF; ++i) s[i] = (double)tmp[i];
