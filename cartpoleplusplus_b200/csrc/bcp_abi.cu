@@ -134,7 +134,7 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
     if (cfg->manifold_order != 0 || cfg->friction_dirs != 2 || !cfg->cone_friction) h->use_split = 0;
     if (h->use_split) {
       A((void**)&h->split.recs, bcp::split_record_words(h->p32) * N * sizeof(float));
-      A((void**)&h->split.queue, N * sizeof(int));
+      A((void**)&h->split.queue, N * 2 * sizeof(int));  // {env, contact counts} per entry
       A((void**)&h->split.qc, bcp::split_counter_words(h->p32) * sizeof(int));
       for (int k = 0; k < 2; ++k) {
         A((void**)&h->split.bins[k], bcp::split_bins_words(h->p32) * sizeof(int));

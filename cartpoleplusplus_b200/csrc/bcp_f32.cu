@@ -1,4 +1,5 @@
 // FP32 fast mode: FMA contraction allowed (compiled with default -fmad=true).
+#include <cstdlib>
 #include "bcp_launch_impl.cuh"
 #include "bcp_split.cuh"
 namespace bcp {
@@ -33,7 +34,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   // k_solve: persistent, as many blocks as stay resident (shared-memory columns bound it)
   LaunchShape L = shape_for(P, N, false);
   // lane-major columns of float4: stride / 4 odd => conflict-free 16-byte accesses
-  const int col4 = (solve_layout(P).words >> 2) | 1;
+  const int col4 = (rec_words >> 2) | 1;  // a column holds the whole record (header + rows)
   const int col_stride = col4 * 4;
   L.smem = (size_t)col_stride * L.block * sizeof(float);
   err = allow_smem(k_solve<float, FRICTION>, L.smem);
@@ -49,17 +50,24 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
     if (per_sm < 1) per_sm = 1;
     per_sm_smem = L.smem;
   }
+  static int fetch_min = 0;
+  if (!fetch_min) {
+    const char* fm = getenv("BCP_FETCH_MIN");
+    fetch_min = fm ? atoi(fm) : kFetchMin;
+    if (fetch_min < 1) fetch_min = 1;
+    if (fetch_min > 32) fetch_min = 32;
+  }
   const int solve_grid = min(sms * per_sm, (N + L.block - 1) / L.block);
   const int prep_grid = (N + kBlock - 1) / kBlock;
   mark();
   for (int k = 0; k <= RS; ++k) {
     const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
     int* qc = b.qc + (size_t)(k < RS ? k : 0) * Q_WORDS;
-    k_prep<float, FRICTION><<<prep_grid, kBlock, 0, s>>>(P, f, id, b.recs, rec_words, b.queue, qc, io, st, vo, s_fin, s_set);
+    k_prep<float, FRICTION><<<prep_grid, kBlock, 0, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
     if (launches) ++*launches;
     mark();
     if (k < RS) {
-      k_solve<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, b.queue, qc, col_stride);
+      k_solve<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc, col_stride, fetch_min);
       if (launches) ++*launches;
       mark();
     }

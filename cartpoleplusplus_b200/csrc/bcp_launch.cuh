@@ -29,7 +29,7 @@ template <typename T> struct Launch {
 
 // Split pipeline of the fast path (bcp_split.cuh), fp32 only: one call of every env as
 // 2*R*S+1 launches.  `recs` holds num_envs solve records of split_record_words() floats,
-// `queue` num_envs ints, `qc` split_counter_words() ints.
+// `queue` 2 * num_envs ints, `qc` split_counter_words() ints.
 struct SplitBuffers {
   float* recs;
   int* queue;

@@ -47,6 +47,14 @@ template <> __device__ __forceinline__ void ld4<float>(const float* p, float o[4
   o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
 }
 #endif
+template <typename T> BCP_HD void st4(T* p, const T v[4]) {
+  p[0] = v[0]; p[1] = v[1]; p[2] = v[2]; p[3] = v[3];
+}
+#if defined(__CUDA_ARCH__)
+template <> __device__ __forceinline__ void st4<float>(float* p, const float v[4]) {
+  *reinterpret_cast<float4*>(p) = make_float4(v[0], v[1], v[2], v[3]);
+}
+#endif
 // reciprocal / reciprocal square root for the residual and the cone scale: one MUFU each on
 // the device (2 ulp; neither feeds a clamp decision), exact on the host and in double
 BCP_HD float fast_rcp(float x) {
@@ -271,9 +279,12 @@ BCP_HD T put_row1(const Params<T>& P, T* row, FBody<T>& B, const T pb[3], const 
   const T den = ang_denom(B, j) + B.invM * dot3(d, d) + cfm;
   const T invD = (den > Lim<T>::eps()) ? T(1.0) / den : T(0.0);
   const T rel_vel = dot3(j, B.wl) + dot3(d, B.v);
-  for (int i = 0; i < 3; ++i) { row[S1_J + i] = j[i]; row[S1_D + i] = d[i]; }
-  row[S1_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
-  row[S1_INVD] = invD;
+  T w[SW1];  // assembled in registers, stored as whole 16-byte pieces
+  for (int i = 0; i < 3; ++i) { w[S1_J + i] = j[i]; w[S1_D + i] = d[i]; }
+  w[S1_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
+  w[S1_INVD] = invD;
+  st4(row, w);
+  st4(row + 4, w + 4);
   if (warm_impulse != T(0.0)) {
     for (int i = 0; i < 3; ++i) { B.dwl[i] += j[i] * B.invI[i] * warm_impulse; B.dv[i] += d[i] * (B.invM * warm_impulse); }
   }
@@ -290,10 +301,14 @@ BCP_HD T put_row2(const Params<T>& P, T* row, FBody<T>& A, FBody<T>& B, const T 
   const T den = (ang_denom(A, ja) + A.invM * nn) + (ang_denom(B, jb) + B.invM * nn) + cfm;
   const T invD = (den > Lim<T>::eps()) ? T(1.0) / den : T(0.0);
   const T rel_vel = (dot3(ja, A.wl) + dot3(axis, A.v)) + (dot3(jb, B.wl) - dot3(axis, B.v));
-  for (int i = 0; i < 3; ++i) { row[S2_JA + i] = ja[i]; row[S2_JB + i] = jb[i]; row[S2_N + i] = axis[i]; }
-  row[S2_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
-  row[S2_INVD] = invD;
-  row[11] = 0;
+  T w[SW2];
+  for (int i = 0; i < 3; ++i) { w[S2_JA + i] = ja[i]; w[S2_JB + i] = jb[i]; w[S2_N + i] = axis[i]; }
+  w[S2_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
+  w[S2_INVD] = invD;
+  w[11] = 0;
+  st4(row, w);
+  st4(row + 4, w + 4);
+  st4(row + 8, w + 8);
   if (warm_impulse != T(0.0)) {
     for (int i = 0; i < 3; ++i) {
       A.dwl[i] += ja[i] * A.invI[i] * warm_impulse; A.dv[i] += axis[i] * (A.invM * warm_impulse);

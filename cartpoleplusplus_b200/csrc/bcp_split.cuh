@@ -64,6 +64,8 @@ BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
     fbody_begin(P, st.cart, P.cart, cbox.R, st.pend_f, st.pend_t, cart);
     fbody_begin(P, st.pole, P.pole, pbox.R, zero3, zero3, pole);
   }
+  T apn_all[N_SLOTS];
+  for (int k = 0; k < N_SLOTS; ++k) apn_all[k] = T(0.0);
   for (int m = 0; m < 3; ++m) {
     BCP_WARP_SYNC();
     if (on) {
@@ -75,7 +77,7 @@ BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
       for (int k = 0; k < nc; ++k) manifold_add(st.mani[m], A, B, cs[k], P.breaking[m]);
       manifold_refresh(st.mani[m], A, B, P.breaking[m], wp);
       T* rows = rec + REC_ROWS + L.base[m];
-      T* apn = rec + REC_APN + slot_of_pair(m);
+      T* apn = apn_all + slot_of_pair(m);
       if (m == BCP_PAIR_GROUND_CART) put_rows<T, FRICTION, false>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, cart, cart);
       else if (m == BCP_PAIR_CART_POLE) put_rows<T, FRICTION, true>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, cart, pole);
       else put_rows<T, FRICTION, false>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, pole, pole);
@@ -86,45 +88,59 @@ BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
     rec[REC_C_GC] = as_real(st.mani[BCP_PAIR_GROUND_CART].count, T(0));
     rec[REC_C_CP] = as_real(st.mani[BCP_PAIR_CART_POLE].count, T(0));
     rec[REC_C_GP] = as_real(st.mani[BCP_PAIR_GROUND_POLE].count, T(0));
+    T d[12];
     for (int i = 0; i < 3; ++i) {  // warm-start deltas
-      rec[REC_DVEL + i] = cart.dwl[i]; rec[REC_DVEL + 3 + i] = cart.dv[i];
-      rec[REC_DVEL + 6 + i] = pole.dwl[i]; rec[REC_DVEL + 9 + i] = pole.dv[i];
+      d[i] = cart.dwl[i]; d[3 + i] = cart.dv[i];
+      d[6 + i] = pole.dwl[i]; d[9 + i] = pole.dv[i];
       st.cart.w[i] = cart.wl[i]; st.cart.v[i] = cart.v[i];
       st.pole.w[i] = pole.wl[i]; st.pole.v[i] = pole.v[i];
       st.pend_f[i] = 0; st.pend_t[i] = 0;  // clearForcesAndTorques
     }
+    for (int k = 0; k < 3; ++k) { st4(rec + REC_DVEL + 4 * k, d + 4 * k); st4(rec + REC_APN + 4 * k, apn_all + 4 * k); }
   }
 }
 
 // what a lane needs to start a solve: contact counts, warm-start deltas and impulses
-template <typename T> BCP_HD void solve_begin(const Params<T>& P, const T* rec, int cnt[3], SolveRegs<T>& R) {
-  cnt[0] = as_int(rec[REC_C_GC]); cnt[1] = as_int(rec[REC_C_CP]); cnt[2] = as_int(rec[REC_C_GP]);
+template <typename T> BCP_HD void solve_consts(const Params<T>& P, SolveRegs<T>& R) {
   for (int i = 0; i < 3; ++i) {
-    R.cart.dwl[i] = rec[REC_DVEL + i]; R.cart.dv[i] = rec[REC_DVEL + 3 + i];
-    R.pole.dwl[i] = rec[REC_DVEL + 6 + i]; R.pole.dv[i] = rec[REC_DVEL + 9 + i];
     R.cart.invI[i] = T(1.0) / P.cart.I[i];
     R.pole.invI[i] = T(1.0) / P.pole.I[i];
   }
   R.cart.invM = P.cart.inv_mass;
   R.pole.invM = P.pole.inv_mass;
+}
+template <typename T> BCP_HD void solve_load(const T* rec, int cnt[3], SolveRegs<T>& R) {
+  T h[4], d[12], a[12];
+  ld4(rec, h);
+  for (int k = 0; k < 3; ++k) { ld4(rec + REC_DVEL + 4 * k, d + 4 * k); ld4(rec + REC_APN + 4 * k, a + 4 * k); }
+  cnt[0] = as_int(h[REC_C_GC]); cnt[1] = as_int(h[REC_C_CP]); cnt[2] = as_int(h[REC_C_GP]);
+  for (int i = 0; i < 3; ++i) {
+    R.cart.dwl[i] = d[i]; R.cart.dv[i] = d[3 + i];
+    R.pole.dwl[i] = d[6 + i]; R.pole.dv[i] = d[9 + i];
+  }
 #pragma unroll
   for (int s = 0; s < N_SLOTS; ++s) {
     const int m = s >> 2, j = s & 3;  // SLOT_* = pair * 4
-    R.apn[s] = (j < cnt[m]) ? rec[REC_APN + s] : T(0.0);
+    R.apn[s] = (j < cnt[m]) ? a[s] : T(0.0);
     R.apf[s][0] = 0;
     R.apf[s][1] = 0;
   }
 }
-// solve results -> record: iteration count, velocity deltas, applied normal impulses
+template <typename T> BCP_HD void solve_begin(const Params<T>& P, const T* rec, int cnt[3], SolveRegs<T>& R) {
+  solve_consts(P, R);
+  solve_load(rec, cnt, R);
+}
+// solve results -> record: iteration count, velocity deltas, applied normal impulses (slots
+// past the contact count hold 0 and are never read back)
 template <typename T> BCP_HD void solve_end(T* rec, const int cnt[3], int iters, const SolveRegs<T>& R) {
+  (void)cnt;
   rec[REC_ITERS] = as_real(iters, T(0));
+  T d[12];
   for (int i = 0; i < 3; ++i) {
-    rec[REC_DVEL + i] = R.cart.dwl[i]; rec[REC_DVEL + 3 + i] = R.cart.dv[i];
-    rec[REC_DVEL + 6 + i] = R.pole.dwl[i]; rec[REC_DVEL + 9 + i] = R.pole.dv[i];
+    d[i] = R.cart.dwl[i]; d[3 + i] = R.cart.dv[i];
+    d[6 + i] = R.pole.dwl[i]; d[9 + i] = R.pole.dv[i];
   }
-#pragma unroll
-  for (int s = 0; s < N_SLOTS; ++s)
-    if ((s & 3) < cnt[s >> 2]) rec[REC_APN + s] = R.apn[s];
+  for (int k = 0; k < 3; ++k) { st4(rec + REC_DVEL + 4 * k, d + 4 * k); st4(rec + REC_APN + 4 * k, R.apn + 4 * k); }
 }
 
 // finish half of a substep: velocities += deltas, integrate, impulses -> manifold cache
@@ -207,11 +223,14 @@ __device__ __forceinline__ int visit(const VisitOrder& vo, int i, int N) {
   return -1;
 }
 
+template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
+  return st.mani[0].count | (st.mani[1].count << 8) | (st.mani[2].count << 16);
+}
 // s_fin: substep to finish (-1: none, this is the first kernel of the call)
 // s_set: substep to set up  (-1: none, this is the last kernel of the call)
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
-                                                 T* __restrict__ recs, int rec_words, int* __restrict__ queue,
+                                                 T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
                                                  int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
                                                  int s_set) {
   const int N = P.num_envs;
@@ -263,8 +282,10 @@ __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Para
     bl = __shfl_sync(0xffffffffu, bl, 0);
     bs = __shfl_sync(0xffffffffu, bs, 0);
     const unsigned lt = (1u << lane) - 1;
-    if (is_long) queue[bl + __popc(ml & lt)] = e;
-    else if (on) queue[N - 1 - (bs + __popc(ms & lt))] = e;
+    // entry = env id + its three contact counts (the solver sizes its copy without the record)
+    const int2 entry = make_int2(e, queue_meta(st));
+    if (is_long) queue[bl + __popc(ml & lt)] = entry;
+    else if (on) queue[N - 1 - (bs + __popc(ms & lt))] = entry;
   } else {  // the call closes: steps / done / reward (:239-260), outputs, episode statistics
     bool live = false;
     const int rs = call_end(P, st, mode, obs, live);
@@ -303,33 +324,62 @@ __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Para
 }
 
 // persistent pooled solve: every lane keeps pulling envs until the queue is dry.
-// Shared memory: one column per lane, lane-major ([lane][col_stride] words, col_stride / 4 odd):
-// conflict-free both for 32 lanes reading the same float4 of their own columns (the sweep) and
-// for 32 lanes writing consecutive float4 of ONE column (the cooperative copy of a record's
-// rows when a lane takes a new env).
-constexpr int kFetchMin = 6;  // idle lanes that trigger a fetch round
+// Shared memory: one column per lane holding a copy of the env's whole solve record, lane-major
+// ([lane][col_stride] words, col_stride / 4 odd): conflict-free for 32 lanes reading the same
+// float4 of their own columns (the sweep).  A lane that takes an env does not wait for it: the
+// warp issues the record -> column copy as 16-byte cp.async (zero-filled for the row slots the
+// env does not use, so the sweep stays branch-free), runs one more iteration of the lanes that
+// are busy, and only then starts the staged lanes.
+constexpr int kFetchMin = 4;  // idle lanes that trigger a fetch round
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, int src_bytes) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(d), "l"(gmem_src), "r"(src_bytes) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
-                                                  const int* __restrict__ queue, int* __restrict__ qc, int col_stride) {
+                                                  const int2* __restrict__ queue, int* __restrict__ qc, int col_stride,
+                                                  int fetch_min) {
   const unsigned FULL = 0xffffffffu;
   T* const smem = reinterpret_cast<T*>(bcp_smem);
   const int lane = threadIdx.x & 31, warp_base = threadIdx.x - lane;
-  const T* const colp = smem + (size_t)threadIdx.x * col_stride;
+  T* const col = smem + (size_t)threadIdx.x * col_stride;
   const SolveLayout L = solve_layout(P);
   const int N = P.num_envs;
   const int n_long = qc[Q_LONG], total = n_long + qc[Q_SHORT];
   const unsigned lt = (1u << lane) - 1;
+  const int rec16 = (rec_words * (int)sizeof(T)) >> 4, hdr16 = (REC_ROWS * (int)sizeof(T)) >> 4;
+  int seg_lo[3], seg_per[3];  // 16-byte pieces: start of each pair's row area, pieces per contact
+#pragma unroll
+  for (int m = 0; m < 3; ++m) {
+    seg_lo[m] = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4;
+    seg_per[m] = (L.rpc[m] * (m == BCP_PAIR_CART_POLE ? (int)SW2 : (int)SW1) * (int)sizeof(T)) >> 4;
+  }
   int w_next = 0, w_end = 0;  // the warp's slice of the queue (uniform)
   bool exhausted = total == 0;
   SolveRegs<T> R;
+  solve_consts(P, R);
   int cnt[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
   int it = 0;
   T* rec = nullptr;
-  bool busy = false;
+  bool busy = false, staged = false;
   while (true) {
+    if (__any_sync(FULL, staged)) {  // copies issued one iteration ago: start those lanes
+      cp_async_wait_all();
+      __syncwarp();
+      if (staged) {
+        solve_load(col, cnt, R);
+        it = 0;
+        busy = true;
+        staged = false;
+      }
+#pragma unroll
+      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
+    }
     const unsigned idle = __ballot_sync(FULL, !busy);
-    if (idle && (idle == FULL || (!exhausted && __popc(idle) >= kFetchMin))) {
+    if (idle && !exhausted && (idle == FULL || __popc(idle) >= fetch_min)) {
       unsigned need = idle;
       int idx = -1;
       while (need && !exhausted) {
@@ -347,38 +397,34 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
         if (b >= total) exhausted = true;
         else { w_next = b; w_end = min(b + kFetchChunk, total); }
       }
-      int env = -1;
+      int env = -1, meta = 0;
       if (idx >= 0) {
-        const int pos = idx < n_long ? idx : N - 1 - (idx - n_long);
-        env = queue[pos];
+        const int2 q = queue[idx < n_long ? idx : N - 1 - (idx - n_long)];
+        env = q.x;
+        meta = q.y;
         rec = recs + (size_t)env * rec_words;
-        solve_begin(P, rec, cnt, R);
-        it = 0;
-        busy = true;
+        staged = true;
       }
-      // the warp copies the rows of every newly taken env into its lane's column, zero rows
-      // in the contact slots the env does not use
       unsigned taken = __ballot_sync(FULL, idx >= 0);
       while (taken) {
         const int src = __ffs(taken) - 1;
         taken &= taken - 1;
-        const int e_src = __shfl_sync(FULL, env, src);
-        const float4* r_src = reinterpret_cast<const float4*>(recs + (size_t)e_src * rec_words + REC_ROWS);
-        float4* c_dst = reinterpret_cast<float4*>(smem + (size_t)(warp_base + src) * col_stride);
+        const int e_src = __shfl_sync(FULL, env, src), m_src = __shfl_sync(FULL, meta, src);
+        const char* r_src = reinterpret_cast<const char*>(recs + (size_t)e_src * rec_words);
+        char* c_dst = reinterpret_cast<char*>(smem + (size_t)(warp_base + src) * col_stride);
+        for (int i = lane; i < rec16; i += 32) {
+          bool live = i < hdr16;
 #pragma unroll
-        for (int m = 0; m < 3; ++m) {
-          const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
-          const int live4 = (__shfl_sync(FULL, cnt[m], src) * L.rpc[m] * w) >> 2, all4 = (4 * L.rpc[m] * w) >> 2;
-          const int b4 = L.base[m] >> 2;
-          for (int i = lane; i < all4; i += 32) c_dst[b4 + i] = (i < live4) ? r_src[b4 + i] : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int m = 0; m < 3; ++m) live = live || (i >= seg_lo[m] && i - seg_lo[m] < ((m_src >> (8 * m)) & 0xff) * seg_per[m]);
+          cp_async16(c_dst + 16 * i, r_src + 16 * i, live ? 16 : 0);
         }
       }
-      __syncwarp();
-#pragma unroll
-      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
     }
-    if (!__any_sync(FULL, busy)) break;
-    const T lsr = solve_iteration<T, FRICTION>(P, colp, L, mx, R);
+    if (!__any_sync(FULL, busy)) {
+      if (!__any_sync(FULL, staged)) break;
+      continue;
+    }
+    const T lsr = solve_iteration<T, FRICTION>(P, col + REC_ROWS, L, mx, R);
     bool conv = false;
     if (busy) {
       it++;
