@@ -18,7 +18,7 @@ LIB = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libbcp.so")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC", "-Xptxas", "-v"]
 UNITS = [
-    ("bcp_f32.cu", []),
+    ("bcp_f32.cu", ["-prec-div=false", "-prec-sqrt=false", "-ftz=true"]),
     ("bcp_f64.cu", ["-fmad=false"]),
     ("bcp_abi.cu", []),
 ]
@@ -56,7 +56,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     def compile_one(unit):
         src, extra = unit
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
-        cmd = [nvcc, *ARCH, *COMMON, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
+        tune = os.environ.get("BCP_NVCC_EXTRA", "").split()  # tuning experiments (-D...), empty in the product build
+        cmd = [nvcc, *ARCH, *COMMON, *extra, *tune, "-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True, env=env)
         with open(obj + ".ptxas.log", "w") as fh:
             fh.write(r.stderr)

@@ -58,12 +58,18 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
     if (fetch_min > 32) fetch_min = 32;
   }
   const int solve_grid = min(sms * per_sm, (N + L.block - 1) / L.block);
-  const int prep_grid = (N + kBlock - 1) / kBlock;
+  static int prep_block = 0;
+  if (!prep_block) {
+    const char* pb = getenv("BCP_PREP_BLOCK");
+    prep_block = pb ? atoi(pb) : kBlock;
+    if (prep_block < 32 || prep_block > kBlock || prep_block % 32) prep_block = kBlock;
+  }
+  const int prep_grid = (N + prep_block - 1) / prep_block;
   mark();
   for (int k = 0; k <= RS; ++k) {
     const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
     int* qc = b.qc + (size_t)(k < RS ? k : 0) * Q_WORDS;
-    k_prep<float, FRICTION><<<prep_grid, kBlock, 0, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
+    k_prep<float, FRICTION><<<prep_grid, prep_block, 0, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
     if (launches) ++*launches;
     mark();
     if (k < RS) {

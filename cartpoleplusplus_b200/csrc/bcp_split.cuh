@@ -226,10 +226,13 @@ __device__ __forceinline__ int visit(const VisitOrder& vo, int i, int N) {
 template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
   return st.mani[0].count | (st.mani[1].count << 8) | (st.mani[2].count << 16);
 }
+#ifndef BCP_PREP_MINB
+#define BCP_PREP_MINB 4  // resident blocks per SM the register budget of k_prep is cut for
+#endif
 // s_fin: substep to finish (-1: none, this is the first kernel of the call)
 // s_set: substep to set up  (-1: none, this is the last kernel of the call)
 template <typename T, bool FRICTION>
-__global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
+__global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
                                                  int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
                                                  int s_set) {
@@ -330,7 +333,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_prep(const __grid_constant__ Para
 // warp issues the record -> column copy as 16-byte cp.async (zero-filled for the row slots the
 // env does not use, so the sweep stays branch-free), runs one more iteration of the lanes that
 // are busy, and only then starts the staged lanes.
-constexpr int kFetchMin = 4;  // idle lanes that trigger a fetch round
+constexpr int kFetchMin = 10;  // idle lanes that trigger a fetch round
 
 __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, int src_bytes) {
   const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
