@@ -54,6 +54,7 @@ template <typename T> struct FBody {
   T wl[3], v[3];    // unconstrained velocities (after forward dynamics)
   T dwl[3], dv[3];  // deltas accumulated by the sweep
   T invI[3], invM;
+  T sI[3];  // sqrt(invI): scale of the angular jacobians in the pooled solver's rows (bcp_solve.cuh)
 };
 
 template <typename T> BCP_HD void fbody_begin(const Params<T>& P, const Body<T>& ob, const BoxP<T>& bp, const T* Rm,
@@ -73,6 +74,7 @@ template <typename T> BCP_HD void fbody_begin(const Params<T>& P, const Body<T>&
     fb.dwl[i] = 0;
     fb.dv[i] = 0;
     fb.invI[i] = T(1.0) / bp.I[i];
+    fb.sI[i] = bsqrt(fb.invI[i]);
   }
   fb.invM = bp.inv_mass;
 }

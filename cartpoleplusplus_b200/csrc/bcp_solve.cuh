@@ -24,15 +24,21 @@ enum { SLOT_GC = 0, SLOT_CP = 4, SLOT_GP = 8, N_SLOTS = 12 };  // applied-impuls
 
 // word offsets of the three pairs' row blocks inside a column / a record's row area
 struct SolveLayout {
-  int base[3], rpc[3], words;
+  int base[3];   // first word of the pair's 4 normal rows (stride SW1 / SW2)
+  int fbase[3];  // first word of the pair's 4 friction-row pairs (stride 2 rows), -1 if none
+  int rpc[3], words;
 };
 template <typename T> BCP_HD SolveLayout solve_layout(const Params<T>& P) {
   SolveLayout L;
   int at = 0;
-  for (int m = 0; m < 3; ++m) {
-    L.base[m] = at;
+  for (int m = 0; m < 3; ++m) {  // normal rows of every pair first: fixed strides, and the
+    L.base[m] = at;              // live part of each block is a prefix (contacts 0..count-1)
     L.rpc[m] = P.rows_per_contact[m];
-    at += 4 * L.rpc[m] * (m == BCP_PAIR_CART_POLE ? (int)SW2 : (int)SW1);
+    at += 4 * (m == BCP_PAIR_CART_POLE ? (int)SW2 : (int)SW1);
+  }
+  for (int m = 0; m < 3; ++m) {
+    L.fbase[m] = L.rpc[m] > 1 ? at : -1;
+    at += 4 * (L.rpc[m] - 1) * (m == BCP_PAIR_CART_POLE ? (int)SW2 : (int)SW1);
   }
   L.words = at;
   return L;
@@ -45,6 +51,16 @@ template <typename T> BCP_HD void ld4(const T* p, T o[4]) {
 template <> __device__ __forceinline__ void ld4<float>(const float* p, float o[4]) {
   const float4 v = *reinterpret_cast<const float4*>(p);
   o[0] = v.x; o[1] = v.y; o[2] = v.z; o[3] = v.w;
+}
+#endif
+// row load of the solver sweep.  SMEM (the pooled kernel: `p` is a shared-memory column): a
+// volatile ld.shared, which the compiler keeps where it is written - one row AHEAD of its use -
+// instead of sinking it below the warp-uniform loop exits next to the first consumer.
+template <bool SMEM, typename T> BCP_HD void ld4_row(const T* p, T o[4]) { ld4(p, o); }
+#if defined(__CUDA_ARCH__)
+template <> __device__ __forceinline__ void ld4_row<true, float>(const float* p, float o[4]) {
+  const unsigned a = (unsigned)__cvta_generic_to_shared(p);
+  asm volatile("ld.volatile.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(o[0]), "=f"(o[1]), "=f"(o[2]), "=f"(o[3]) : "r"(a));
 }
 #endif
 template <typename T> BCP_HD void st4(T* p, const T v[4]) {
@@ -82,9 +98,11 @@ BCP_HD float bmax(float a, float b) { return fmaxf(a, b); }
 BCP_HD double bmin(double a, double b) { return fmin(a, b); }
 BCP_HD double bmax(double a, double b) { return fmax(a, b); }
 
-// solver-side body: deltas only, plus the constants M^-1 is made of
+// solver-side body.  Angular deltas are kept SCALED, wt = dw_local / sqrt(invI) per axis, and the
+// rows hold angular jacobians scaled the other way (j * sqrt(invI)): J.dw and the update
+// dw += invI j delta become plain dot products / FMAs without the per-row invI multiplies.
 template <typename T> struct SBodyLite {
-  T dwl[3], dv[3], invI[3], invM;
+  T wt[3], dv[3], invM;
 };
 // everything a lane carries through a solve
 template <typename T> struct SolveRegs {
@@ -92,43 +110,45 @@ template <typename T> struct SolveRegs {
   T apn[N_SLOTS];     // applied normal impulses
   T apf[N_SLOTS][2];  // applied friction impulses
 };
-
-// clamp the accumulated impulse; returns the residual of the row
-template <typename T> BCP_HD T clamp_row(T& ap, T& delta, T u, T invD, T lo, T hi) {
-  const T sum = ap + delta;
-  const T nv = bmin(bmax(sum, lo), hi);
-  delta = nv - ap;
-  ap = nv;
-  return (nv != sum) ? delta * fast_rcp(invD) : u;
+template <typename T> struct SRow1 { T a[4], b[4]; };        // a = j0 j1 j2 d0 | b = d1 d2 rhsV invD
+template <typename T> struct SRow2 { T a[4], b[4], c[4]; };  // a = ja0 ja1 ja2 jb0 | b = jb1 jb2 n0 n1 | c = n2 rhsV invD -
+template <bool SMEM, typename T> BCP_HD void load_row(const T* p, SRow1<T>& r) { ld4_row<SMEM>(p, r.a); ld4_row<SMEM>(p + 4, r.b); }
+template <bool SMEM, typename T> BCP_HD void load_row(const T* p, SRow2<T>& r) {
+  ld4_row<SMEM>(p, r.a); ld4_row<SMEM>(p + 4, r.b); ld4_row<SMEM>(p + 8, r.c);
 }
 
-template <typename T> BCP_HD T solve_row1(const Params<T>& P, const T* row, SBodyLite<T>& B, T& ap, T lo, T hi, T cfm) {
-  T a[4], b[4];
-  ld4(row, a);
-  ld4(row + 4, b);  // a = j0 j1 j2 d0 | b = d1 d2 rhsV invD
-  const T jdv = (a[0] * B.dwl[0] + a[1] * B.dwl[1] + a[2] * B.dwl[2]) + (a[3] * B.dv[0] + b[0] * B.dv[1] + b[1] * B.dv[2]);
+// normal row: accumulated impulse clamped at 0 from below (Bullet's upper limit of 1e10 is
+// never reached by a finite state); returns the residual of the row
+template <typename T> BCP_HD T clamp_normal(T& ap, T& delta, T u, T D) {  // D = 1 / invD
+  const T sum = ap + delta;
+  const T nv = bmax(sum, T(0.0));
+  delta = nv - ap;
+  ap = nv;
+  return (nv != sum) ? delta * D : u;
+}
+template <typename T> BCP_HD T solve_row1(const SRow1<T>& r, SBodyLite<T>& B, T& ap, T cfm) {
+  const T* a = r.a; const T* b = r.b;
+  const T D = fast_rcp(b[3]);  // off the dependent chain: issued with the row's first products
+  const T jdv = (a[0] * B.wt[0] + a[1] * B.wt[1] + a[2] * B.wt[2]) + (a[3] * B.dv[0] + b[0] * B.dv[1] + b[1] * B.dv[2]);
   const T u = b[2] - ap * cfm - jdv;
   T delta = u * b[3];
-  const T res = clamp_row(ap, delta, u, b[3], lo, hi);
+  const T res = clamp_normal(ap, delta, u, D);
   const T lm = B.invM * delta;
-  B.dwl[0] += a[0] * (B.invI[0] * delta); B.dwl[1] += a[1] * (B.invI[1] * delta); B.dwl[2] += a[2] * (B.invI[2] * delta);
+  B.wt[0] += a[0] * delta; B.wt[1] += a[1] * delta; B.wt[2] += a[2] * delta;
   B.dv[0] += a[3] * lm; B.dv[1] += b[0] * lm; B.dv[2] += b[1] * lm;
   return res;
 }
-template <typename T>
-BCP_HD T solve_row2(const Params<T>& P, const T* row, SBodyLite<T>& A, SBodyLite<T>& B, T& ap, T lo, T hi, T cfm) {
-  T a[4], b[4], c[4];
-  ld4(row, a);
-  ld4(row + 4, b);
-  ld4(row + 8, c);  // a = ja0 ja1 ja2 jb0 | b = jb1 jb2 n0 n1 | c = n2 rhsV invD -
-  const T jdv = (a[0] * A.dwl[0] + a[1] * A.dwl[1] + a[2] * A.dwl[2]) + (a[3] * B.dwl[0] + b[0] * B.dwl[1] + b[1] * B.dwl[2]) +
+template <typename T> BCP_HD T solve_row2(const SRow2<T>& r, SBodyLite<T>& A, SBodyLite<T>& B, T& ap, T cfm) {
+  const T* a = r.a; const T* b = r.b; const T* c = r.c;
+  const T D = fast_rcp(c[2]);
+  const T jdv = (a[0] * A.wt[0] + a[1] * A.wt[1] + a[2] * A.wt[2]) + (a[3] * B.wt[0] + b[0] * B.wt[1] + b[1] * B.wt[2]) +
                 (b[2] * (A.dv[0] - B.dv[0]) + b[3] * (A.dv[1] - B.dv[1]) + c[0] * (A.dv[2] - B.dv[2]));
   const T u = c[1] - ap * cfm - jdv;
   T delta = u * c[2];
-  const T res = clamp_row(ap, delta, u, c[2], lo, hi);
+  const T res = clamp_normal(ap, delta, u, D);
   const T la = A.invM * delta, lb = B.invM * delta;
-  A.dwl[0] += a[0] * (A.invI[0] * delta); A.dwl[1] += a[1] * (A.invI[1] * delta); A.dwl[2] += a[2] * (A.invI[2] * delta);
-  B.dwl[0] += a[3] * (B.invI[0] * delta); B.dwl[1] += b[0] * (B.invI[1] * delta); B.dwl[2] += b[1] * (B.invI[2] * delta);
+  A.wt[0] += a[0] * delta; A.wt[1] += a[1] * delta; A.wt[2] += a[2] * delta;
+  B.wt[0] += a[3] * delta; B.wt[1] += b[0] * delta; B.wt[2] += b[1] * delta;
   A.dv[0] += b[2] * la; A.dv[1] += b[3] * la; A.dv[2] += c[0] * la;
   B.dv[0] -= b[2] * lb; B.dv[1] -= b[3] * lb; B.dv[2] -= c[0] * lb;
   return res;
@@ -136,7 +156,7 @@ BCP_HD T solve_row2(const Params<T>& P, const T* row, SBodyLite<T>& A, SBodyLite
 
 // cone clip of the two friction impulses of one contact (resolveConeFrictionConstraintRows)
 template <typename T>
-BCP_HD T cone_clip(T& apA, T& apB, T& dA, T& dB, T uA, T uB, T invDA, T invDB, T L) {
+BCP_HD T cone_clip(T& apA, T& apB, T& dA, T& dB, T uA, T uB, T DA, T DB, T L) {  // DA, DB = 1 / invD
   // Bullet clips (sumA, sumB) to the circle of radius |L| through the angle (sin, cos) =
   // (sumA, sumB) / r; outside the circle both clamps bind, i.e. the pair is scaled by |L| / r
   const T sumA = apA + dA, sumB = apB + dB;
@@ -148,50 +168,48 @@ BCP_HD T cone_clip(T& apA, T& apB, T& dA, T& dB, T uA, T uB, T invDA, T invDB, T
   dB = nB - apB;
   apA = nA;
   apB = nB;
-  const T rA = clip ? dA * fast_rcp(invDA) : uA;
-  const T rB = clip ? dB * fast_rcp(invDB) : uB;
+  const T rA = clip ? dA * DA : uA;
+  const T rB = clip ? dB * DB : uB;
   return rA + rB;
 }
-template <typename T> BCP_HD T solve_cone1(const Params<T>& P, const T* rowA, SBodyLite<T>& B, T& apA, T& apB, T L, T cfm) {
-  const T* rowB = rowA + SW1;
-  T a[4], b[4], c[4], d[4];
-  ld4(rowA, a); ld4(rowA + 4, b); ld4(rowB, c); ld4(rowB + 4, d);
-  const T jdvB = (c[0] * B.dwl[0] + c[1] * B.dwl[1] + c[2] * B.dwl[2]) + (c[3] * B.dv[0] + d[0] * B.dv[1] + d[1] * B.dv[2]);
-  const T jdvA = (a[0] * B.dwl[0] + a[1] * B.dwl[1] + a[2] * B.dwl[2]) + (a[3] * B.dv[0] + b[0] * B.dv[1] + b[1] * B.dv[2]);
+template <typename T> BCP_HD T solve_cone1(const SRow1<T>& ra, const SRow1<T>& rb, SBodyLite<T>& B, T& apA, T& apB, T L, T cfm) {
+  const T* a = ra.a; const T* b = ra.b; const T* c = rb.a; const T* d = rb.b;
+  const T DA = fast_rcp(b[3]), DB = fast_rcp(d[3]);
+  const T jdvB = (c[0] * B.wt[0] + c[1] * B.wt[1] + c[2] * B.wt[2]) + (c[3] * B.dv[0] + d[0] * B.dv[1] + d[1] * B.dv[2]);
+  const T jdvA = (a[0] * B.wt[0] + a[1] * B.wt[1] + a[2] * B.wt[2]) + (a[3] * B.dv[0] + b[0] * B.dv[1] + b[1] * B.dv[2]);
   const T uB = d[2] - apB * cfm - jdvB, uA = b[2] - apA * cfm - jdvA;
   T dB = uB * d[3], dA = uA * b[3];
-  const T res = cone_clip(apA, apB, dA, dB, uA, uB, b[3], d[3], L);
+  const T res = cone_clip(apA, apB, dA, dB, uA, uB, DA, DB, L);
   const T lA = B.invM * dA, lB = B.invM * dB;
-  B.dwl[0] += a[0] * (B.invI[0] * dA); B.dwl[1] += a[1] * (B.invI[1] * dA); B.dwl[2] += a[2] * (B.invI[2] * dA);
+  B.wt[0] += a[0] * dA; B.wt[1] += a[1] * dA; B.wt[2] += a[2] * dA;
   B.dv[0] += a[3] * lA; B.dv[1] += b[0] * lA; B.dv[2] += b[1] * lA;
-  B.dwl[0] += c[0] * (B.invI[0] * dB); B.dwl[1] += c[1] * (B.invI[1] * dB); B.dwl[2] += c[2] * (B.invI[2] * dB);
+  B.wt[0] += c[0] * dB; B.wt[1] += c[1] * dB; B.wt[2] += c[2] * dB;
   B.dv[0] += c[3] * lB; B.dv[1] += d[0] * lB; B.dv[2] += d[1] * lB;
   return res;
 }
 template <typename T>
-BCP_HD T solve_cone2(const Params<T>& P, const T* rowA, SBodyLite<T>& A, SBodyLite<T>& B, T& apA, T& apB, T L, T cfm) {
-  const T* rowB = rowA + SW2;
-  T a[4], b[4], c[4], e[4], f[4], g[4];
-  ld4(rowA, a); ld4(rowA + 4, b); ld4(rowA + 8, c); ld4(rowB, e); ld4(rowB + 4, f); ld4(rowB + 8, g);
+BCP_HD T solve_cone2(const SRow2<T>& ra, const SRow2<T>& rb, SBodyLite<T>& A, SBodyLite<T>& B, T& apA, T& apB, T L, T cfm) {
+  const T* a = ra.a; const T* b = ra.b; const T* c = ra.c; const T* e = rb.a; const T* f = rb.b; const T* g = rb.c;
+  const T DA = fast_rcp(c[2]), DB = fast_rcp(g[2]);
   const T dl[3] = {A.dv[0] - B.dv[0], A.dv[1] - B.dv[1], A.dv[2] - B.dv[2]};
-  const T jdvB = (e[0] * A.dwl[0] + e[1] * A.dwl[1] + e[2] * A.dwl[2]) + (e[3] * B.dwl[0] + f[0] * B.dwl[1] + f[1] * B.dwl[2]) +
+  const T jdvB = (e[0] * A.wt[0] + e[1] * A.wt[1] + e[2] * A.wt[2]) + (e[3] * B.wt[0] + f[0] * B.wt[1] + f[1] * B.wt[2]) +
                  (f[2] * dl[0] + f[3] * dl[1] + g[0] * dl[2]);
-  const T jdvA = (a[0] * A.dwl[0] + a[1] * A.dwl[1] + a[2] * A.dwl[2]) + (a[3] * B.dwl[0] + b[0] * B.dwl[1] + b[1] * B.dwl[2]) +
+  const T jdvA = (a[0] * A.wt[0] + a[1] * A.wt[1] + a[2] * A.wt[2]) + (a[3] * B.wt[0] + b[0] * B.wt[1] + b[1] * B.wt[2]) +
                  (b[2] * dl[0] + b[3] * dl[1] + c[0] * dl[2]);
   const T uB = g[1] - apB * cfm - jdvB, uA = c[1] - apA * cfm - jdvA;
   T dB = uB * g[2], dA = uA * c[2];
-  const T res = cone_clip(apA, apB, dA, dB, uA, uB, c[2], g[2], L);
+  const T res = cone_clip(apA, apB, dA, dB, uA, uB, DA, DB, L);
   {
     const T la = A.invM * dA, lb = B.invM * dA;
-    A.dwl[0] += a[0] * (A.invI[0] * dA); A.dwl[1] += a[1] * (A.invI[1] * dA); A.dwl[2] += a[2] * (A.invI[2] * dA);
-    B.dwl[0] += a[3] * (B.invI[0] * dA); B.dwl[1] += b[0] * (B.invI[1] * dA); B.dwl[2] += b[1] * (B.invI[2] * dA);
+    A.wt[0] += a[0] * dA; A.wt[1] += a[1] * dA; A.wt[2] += a[2] * dA;
+    B.wt[0] += a[3] * dA; B.wt[1] += b[0] * dA; B.wt[2] += b[1] * dA;
     A.dv[0] += b[2] * la; A.dv[1] += b[3] * la; A.dv[2] += c[0] * la;
     B.dv[0] -= b[2] * lb; B.dv[1] -= b[3] * lb; B.dv[2] -= c[0] * lb;
   }
   {
     const T la = A.invM * dB, lb = B.invM * dB;
-    A.dwl[0] += e[0] * (A.invI[0] * dB); A.dwl[1] += e[1] * (A.invI[1] * dB); A.dwl[2] += e[2] * (A.invI[2] * dB);
-    B.dwl[0] += e[3] * (B.invI[0] * dB); B.dwl[1] += f[0] * (B.invI[1] * dB); B.dwl[2] += f[1] * (B.invI[2] * dB);
+    A.wt[0] += e[0] * dB; A.wt[1] += e[1] * dB; A.wt[2] += e[2] * dB;
+    B.wt[0] += e[3] * dB; B.wt[1] += f[0] * dB; B.wt[2] += f[1] * dB;
     A.dv[0] += f[2] * la; A.dv[1] += f[3] * la; A.dv[2] += g[0] * la;
     B.dv[0] -= f[2] * lb; B.dv[1] -= f[3] * lb; B.dv[2] -= g[0] * lb;
   }
@@ -200,66 +218,85 @@ BCP_HD T solve_cone2(const Params<T>& P, const T* rowA, SBodyLite<T>& A, SBodyLi
 
 // One projected Gauss-Seidel iteration over a lane's column: ground-pole, cart-pole,
 // ground-cart normal rows, then their friction rows (manifold_order 0).  mx[m] = slots to
-// sweep per pair (warp-uniform; a lane's unused slots are zero rows).  Returns the largest
-// squared residual.
-template <typename T, bool FRICTION>
+// sweep per pair (warp-uniform; a lane's unused slots are zero rows).  Every row is loaded one
+// row ahead of its use (the first rows of the three blocks at the top), so the shared-memory
+// latency hides behind the previous row's dependent arithmetic.  Returns the largest squared
+// residual.
+template <typename T, bool FRICTION, bool SMEM = false>
 BCP_HD T solve_iteration(const Params<T>& P, const T* colp, const SolveLayout& L, const int mx[3], SolveRegs<T>& R) {
   T lsr = 0;
-  const T cfm_n = P.cfm_normal, cfm_f = P.cfm_friction, big = T(1e10f);
+  const T cfm_n = P.cfm_normal, cfm_f = P.cfm_friction;
 #define BCP_ACC(r_) { const T r__ = (r_); const T r2__ = r__ * r__; lsr = (lsr > r2__) ? lsr : r2__; }
-  {
-    const int st = L.rpc[BCP_PAIR_GROUND_POLE] * SW1;
-    const T* row = colp + L.base[BCP_PAIR_GROUND_POLE];
+  const T* const gp = colp + L.base[BCP_PAIR_GROUND_POLE];
+  const T* const cp = colp + L.base[BCP_PAIR_CART_POLE];
+  const T* const gc = colp + L.base[BCP_PAIR_GROUND_CART];
+  SRow1<T> r_gp, r_gc;
+  SRow2<T> r_cp;
+  load_row<SMEM>(gp, r_gp);
+  load_row<SMEM>(cp, r_cp);
+  load_row<SMEM>(gc, r_gc);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
-      BCP_ACC(solve_row1(P, row + j * st, R.pole, R.apn[SLOT_GP + j], T(0.0), big, cfm_n));
-    }
+  for (int j = 0; j < 4; ++j) {
+    if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
+    const SRow1<T> cur = r_gp;
+    if (j < 3) load_row<SMEM>(gp + (j + 1) * SW1, r_gp);
+    BCP_ACC(solve_row1(cur, R.pole, R.apn[SLOT_GP + j], cfm_n));
   }
-  {
-    const int st = L.rpc[BCP_PAIR_CART_POLE] * SW2;
-    const T* row = colp + L.base[BCP_PAIR_CART_POLE];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (j >= mx[BCP_PAIR_CART_POLE]) break;
-      BCP_ACC(solve_row2(P, row + j * st, R.cart, R.pole, R.apn[SLOT_CP + j], T(0.0), big, cfm_n));
-    }
+  for (int j = 0; j < 4; ++j) {
+    if (j >= mx[BCP_PAIR_CART_POLE]) break;
+    const SRow2<T> cur = r_cp;
+    if (j < 3) load_row<SMEM>(cp + (j + 1) * SW2, r_cp);
+    BCP_ACC(solve_row2(cur, R.cart, R.pole, R.apn[SLOT_CP + j], cfm_n));
   }
-  {
-    const int st = L.rpc[BCP_PAIR_GROUND_CART] * SW1;
-    const T* row = colp + L.base[BCP_PAIR_GROUND_CART];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      if (j >= mx[BCP_PAIR_GROUND_CART]) break;
-      BCP_ACC(solve_row1(P, row + j * st, R.cart, R.apn[SLOT_GC + j], T(0.0), big, cfm_n));
-    }
+  for (int j = 0; j < 4; ++j) {
+    if (j >= mx[BCP_PAIR_GROUND_CART]) break;
+    const SRow1<T> cur = r_gc;
+    if (j < 3) load_row<SMEM>(gc + (j + 1) * SW1, r_gc);
+    BCP_ACC(solve_row1(cur, R.cart, R.apn[SLOT_GC + j], cfm_n));
   }
   if (FRICTION) {
-    if (L.rpc[BCP_PAIR_GROUND_POLE] == 3) {
-      const T* row = colp + L.base[BCP_PAIR_GROUND_POLE] + SW1;
+    if (L.fbase[BCP_PAIR_GROUND_POLE] >= 0 && mx[BCP_PAIR_GROUND_POLE] > 0) {
+      const T* row = colp + L.fbase[BCP_PAIR_GROUND_POLE];
       const T mu = P.mu[BCP_PAIR_GROUND_POLE];
+      SRow1<T> na, nb;
+      load_row<SMEM>(row, na);
+      load_row<SMEM>(row + SW1, nb);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
-        BCP_ACC(solve_cone1(P, row + j * 3 * SW1, R.pole, R.apf[SLOT_GP + j][0], R.apf[SLOT_GP + j][1], mu * R.apn[SLOT_GP + j], cfm_f));
+        const SRow1<T> ca = na, cb = nb;
+        if (j < 3) { load_row<SMEM>(row + (j + 1) * 2 * SW1, na); load_row<SMEM>(row + (j + 1) * 2 * SW1 + SW1, nb); }
+        BCP_ACC(solve_cone1(ca, cb, R.pole, R.apf[SLOT_GP + j][0], R.apf[SLOT_GP + j][1], mu * R.apn[SLOT_GP + j], cfm_f));
       }
     }
-    if (L.rpc[BCP_PAIR_CART_POLE] == 3) {
-      const T* row = colp + L.base[BCP_PAIR_CART_POLE] + SW2;
+    if (L.fbase[BCP_PAIR_CART_POLE] >= 0 && mx[BCP_PAIR_CART_POLE] > 0) {
+      const T* row = colp + L.fbase[BCP_PAIR_CART_POLE];
       const T mu = P.mu[BCP_PAIR_CART_POLE];
+      SRow2<T> na, nb;
+      load_row<SMEM>(row, na);
+      load_row<SMEM>(row + SW2, nb);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         if (j >= mx[BCP_PAIR_CART_POLE]) break;
-        BCP_ACC(solve_cone2(P, row + j * 3 * SW2, R.cart, R.pole, R.apf[SLOT_CP + j][0], R.apf[SLOT_CP + j][1], mu * R.apn[SLOT_CP + j], cfm_f));
+        const SRow2<T> ca = na, cb = nb;
+        if (j < 3) { load_row<SMEM>(row + (j + 1) * 2 * SW2, na); load_row<SMEM>(row + (j + 1) * 2 * SW2 + SW2, nb); }
+        BCP_ACC(solve_cone2(ca, cb, R.cart, R.pole, R.apf[SLOT_CP + j][0], R.apf[SLOT_CP + j][1], mu * R.apn[SLOT_CP + j], cfm_f));
       }
     }
-    if (L.rpc[BCP_PAIR_GROUND_CART] == 3) {
-      const T* row = colp + L.base[BCP_PAIR_GROUND_CART] + SW1;
+    if (L.fbase[BCP_PAIR_GROUND_CART] >= 0 && mx[BCP_PAIR_GROUND_CART] > 0) {
+      const T* row = colp + L.fbase[BCP_PAIR_GROUND_CART];
       const T mu = P.mu[BCP_PAIR_GROUND_CART];
+      SRow1<T> na, nb;
+      load_row<SMEM>(row, na);
+      load_row<SMEM>(row + SW1, nb);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         if (j >= mx[BCP_PAIR_GROUND_CART]) break;
-        BCP_ACC(solve_cone1(P, row + j * 3 * SW1, R.cart, R.apf[SLOT_GC + j][0], R.apf[SLOT_GC + j][1], mu * R.apn[SLOT_GC + j], cfm_f));
+        const SRow1<T> ca = na, cb = nb;
+        if (j < 3) { load_row<SMEM>(row + (j + 1) * 2 * SW1, na); load_row<SMEM>(row + (j + 1) * 2 * SW1 + SW1, nb); }
+        BCP_ACC(solve_cone1(ca, cb, R.cart, R.apf[SLOT_GC + j][0], R.apf[SLOT_GC + j][1], mu * R.apn[SLOT_GC + j], cfm_f));
       }
     }
   }
@@ -280,7 +317,7 @@ BCP_HD T put_row1(const Params<T>& P, T* row, FBody<T>& B, const T pb[3], const 
   const T invD = (den > Lim<T>::eps()) ? T(1.0) / den : T(0.0);
   const T rel_vel = dot3(j, B.wl) + dot3(d, B.v);
   T w[SW1];  // assembled in registers, stored as whole 16-byte pieces
-  for (int i = 0; i < 3; ++i) { w[S1_J + i] = j[i]; w[S1_D + i] = d[i]; }
+  for (int i = 0; i < 3; ++i) { w[S1_J + i] = j[i] * B.sI[i]; w[S1_D + i] = d[i]; }
   w[S1_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
   w[S1_INVD] = invD;
   st4(row, w);
@@ -302,7 +339,7 @@ BCP_HD T put_row2(const Params<T>& P, T* row, FBody<T>& A, FBody<T>& B, const T 
   const T invD = (den > Lim<T>::eps()) ? T(1.0) / den : T(0.0);
   const T rel_vel = (dot3(ja, A.wl) + dot3(axis, A.v)) + (dot3(jb, B.wl) - dot3(axis, B.v));
   T w[SW2];
-  for (int i = 0; i < 3; ++i) { w[S2_JA + i] = ja[i]; w[S2_JB + i] = jb[i]; w[S2_N + i] = axis[i]; }
+  for (int i = 0; i < 3; ++i) { w[S2_JA + i] = ja[i] * A.sI[i]; w[S2_JB + i] = jb[i] * B.sI[i]; w[S2_N + i] = axis[i]; }
   w[S2_RHSV] = (invD > T(0.0)) ? row_rhs(P, rel_vel, dist, rest, T(-1.0), is_friction) : T(0.0);
   w[S2_INVD] = invD;
   w[11] = 0;
@@ -317,26 +354,28 @@ BCP_HD T put_row2(const Params<T>& P, T* row, FBody<T>& A, FBody<T>& B, const T 
   }
   return warm_impulse;
 }
-// rows of manifold m (normal row, then the friction rows along btPlaneSpace1(normal)) and the
-// warm-start impulses of its normal rows into apn[4]
+// rows of manifold m - normal rows into the pair's normal block, the friction rows along
+// btPlaneSpace1(normal) pairwise into its friction block - and the warm-start impulses of the
+// normal rows into apn[4]
 template <typename T, bool FRICTION, bool TWO>
-BCP_HD void put_rows(const Params<T>& P, T* rows, T* apn, int m, int rpc, const Manifold<T>& mf, const WorldPt<T>* wp,
+BCP_HD void put_rows(const Params<T>& P, T* nrows, T* frows, T* apn, int m, int rpc, const Manifold<T>& mf, const WorldPt<T>* wp,
                      FBody<T>& A, FBody<T>& B) {
   const int W = TWO ? (int)SW2 : (int)SW1;
   const T rest = P.rest[m];
   for (int j = 0; j < mf.count; ++j) {
-    T* row = rows + j * rpc * W;
+    T* row = nrows + j * W;
     const T warm = (P.warmstart > T(0.0)) ? mf.p[j].imp * P.warmstart : T(0.0);
     if (TWO) apn[j] = put_row2(P, row, A, B, wp[j].pa, wp[j].pb, mf.p[j].n, mf.p[j].dist, rest, false, warm);
     else apn[j] = put_row1(P, row, B, wp[j].pb, mf.p[j].n, mf.p[j].dist, rest, false, warm);
     if (FRICTION && rpc > 1) {
       T d1[3], d2[3];
       plane_space(mf.p[j].n, d1, d2);
-      if (TWO) put_row2(P, row + W, A, B, wp[j].pa, wp[j].pb, d1, T(0), rest, true, T(0));
-      else put_row1(P, row + W, B, wp[j].pb, d1, T(0), rest, true, T(0));
+      T* fr = frows + j * (rpc - 1) * W;
+      if (TWO) put_row2(P, fr, A, B, wp[j].pa, wp[j].pb, d1, T(0), rest, true, T(0));
+      else put_row1(P, fr, B, wp[j].pb, d1, T(0), rest, true, T(0));
       if (rpc > 2) {
-        if (TWO) put_row2(P, row + 2 * W, A, B, wp[j].pa, wp[j].pb, d2, T(0), rest, true, T(0));
-        else put_row1(P, row + 2 * W, B, wp[j].pb, d2, T(0), rest, true, T(0));
+        if (TWO) put_row2(P, fr + W, A, B, wp[j].pa, wp[j].pb, d2, T(0), rest, true, T(0));
+        else put_row1(P, fr + W, B, wp[j].pb, d2, T(0), rest, true, T(0));
       }
     }
   }

@@ -77,10 +77,11 @@ BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
       for (int k = 0; k < nc; ++k) manifold_add(st.mani[m], A, B, cs[k], P.breaking[m]);
       manifold_refresh(st.mani[m], A, B, P.breaking[m], wp);
       T* rows = rec + REC_ROWS + L.base[m];
+      T* frows = rec + REC_ROWS + (L.fbase[m] >= 0 ? L.fbase[m] : 0);
       T* apn = apn_all + slot_of_pair(m);
-      if (m == BCP_PAIR_GROUND_CART) put_rows<T, FRICTION, false>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, cart, cart);
-      else if (m == BCP_PAIR_CART_POLE) put_rows<T, FRICTION, true>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, cart, pole);
-      else put_rows<T, FRICTION, false>(P, rows, apn, m, L.rpc[m], st.mani[m], wp, pole, pole);
+      if (m == BCP_PAIR_GROUND_CART) put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], st.mani[m], wp, cart, cart);
+      else if (m == BCP_PAIR_CART_POLE) put_rows<T, FRICTION, true>(P, rows, frows, apn, m, L.rpc[m], st.mani[m], wp, cart, pole);
+      else put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], st.mani[m], wp, pole, pole);
     }
   }
   BCP_WARP_SYNC();
@@ -101,22 +102,26 @@ BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
 }
 
 // what a lane needs to start a solve: contact counts, warm-start deltas and impulses
-template <typename T> BCP_HD void solve_consts(const Params<T>& P, SolveRegs<T>& R) {
+// sI = sqrt(invI), rI = sqrt(I) per body axis: in and out of the solver's scaled angular deltas
+template <typename T> struct SolveScale {
+  T cart_sI[3], cart_rI[3], pole_sI[3], pole_rI[3];
+};
+template <typename T> BCP_HD void solve_consts(const Params<T>& P, SolveRegs<T>& R, SolveScale<T>& S) {
   for (int i = 0; i < 3; ++i) {
-    R.cart.invI[i] = T(1.0) / P.cart.I[i];
-    R.pole.invI[i] = T(1.0) / P.pole.I[i];
+    S.cart_sI[i] = bsqrt(T(1.0) / P.cart.I[i]); S.cart_rI[i] = T(1.0) / S.cart_sI[i];
+    S.pole_sI[i] = bsqrt(T(1.0) / P.pole.I[i]); S.pole_rI[i] = T(1.0) / S.pole_sI[i];
   }
   R.cart.invM = P.cart.inv_mass;
   R.pole.invM = P.pole.inv_mass;
 }
-template <typename T> BCP_HD void solve_load(const T* rec, int cnt[3], SolveRegs<T>& R) {
+template <typename T> BCP_HD void solve_load(const T* rec, const SolveScale<T>& S, int cnt[3], SolveRegs<T>& R) {
   T h[4], d[12], a[12];
   ld4(rec, h);
   for (int k = 0; k < 3; ++k) { ld4(rec + REC_DVEL + 4 * k, d + 4 * k); ld4(rec + REC_APN + 4 * k, a + 4 * k); }
   cnt[0] = as_int(h[REC_C_GC]); cnt[1] = as_int(h[REC_C_CP]); cnt[2] = as_int(h[REC_C_GP]);
   for (int i = 0; i < 3; ++i) {
-    R.cart.dwl[i] = d[i]; R.cart.dv[i] = d[3 + i];
-    R.pole.dwl[i] = d[6 + i]; R.pole.dv[i] = d[9 + i];
+    R.cart.wt[i] = d[i] * S.cart_rI[i]; R.cart.dv[i] = d[3 + i];
+    R.pole.wt[i] = d[6 + i] * S.pole_rI[i]; R.pole.dv[i] = d[9 + i];
   }
 #pragma unroll
   for (int s = 0; s < N_SLOTS; ++s) {
@@ -126,19 +131,14 @@ template <typename T> BCP_HD void solve_load(const T* rec, int cnt[3], SolveRegs
     R.apf[s][1] = 0;
   }
 }
-template <typename T> BCP_HD void solve_begin(const Params<T>& P, const T* rec, int cnt[3], SolveRegs<T>& R) {
-  solve_consts(P, R);
-  solve_load(rec, cnt, R);
-}
 // solve results -> record: iteration count, velocity deltas, applied normal impulses (slots
 // past the contact count hold 0 and are never read back)
-template <typename T> BCP_HD void solve_end(T* rec, const int cnt[3], int iters, const SolveRegs<T>& R) {
-  (void)cnt;
+template <typename T> BCP_HD void solve_end(T* rec, const SolveScale<T>& S, int iters, const SolveRegs<T>& R) {
   rec[REC_ITERS] = as_real(iters, T(0));
   T d[12];
   for (int i = 0; i < 3; ++i) {
-    d[i] = R.cart.dwl[i]; d[3 + i] = R.cart.dv[i];
-    d[6 + i] = R.pole.dwl[i]; d[9 + i] = R.pole.dv[i];
+    d[i] = R.cart.wt[i] * S.cart_sI[i]; d[3 + i] = R.cart.dv[i];
+    d[6 + i] = R.pole.wt[i] * S.pole_sI[i]; d[9 + i] = R.pole.dv[i];
   }
   for (int k = 0; k < 3; ++k) { st4(rec + REC_DVEL + 4 * k, d + 4 * k); st4(rec + REC_APN + 4 * k, R.apn + 4 * k); }
 }
@@ -169,14 +169,16 @@ BCP_HD void substep_split_reference(const Params<T>& P, Env<T>& st, T* rec, Subs
   split_setup<T, FRICTION>(P, st, rec, true);
   int cnt[3];
   SolveRegs<T> R;
-  solve_begin(P, rec, cnt, R);
+  SolveScale<T> S;
+  solve_consts(P, R, S);
+  solve_load(rec, S, cnt, R);
   int it = 0;
   for (int k = 0; k < P.solver_iterations; ++k) {
     const T lsr = solve_iteration<T, FRICTION>(P, rec + REC_ROWS, L, cnt, R);
     it = k + 1;
     if (lsr <= P.residual_thr || k >= P.solver_iterations - 1) break;
   }
-  solve_end(rec, cnt, it, R);
+  solve_end(rec, S, it, R);
   split_finish(P, st, rec);
   if (info) {
     info->iterations = it;
@@ -354,16 +356,21 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
   const int n_long = qc[Q_LONG], total = n_long + qc[Q_SHORT];
   const unsigned lt = (1u << lane) - 1;
   const int rec16 = (rec_words * (int)sizeof(T)) >> 4, hdr16 = (REC_ROWS * (int)sizeof(T)) >> 4;
-  int seg_lo[3], seg_per[3];  // 16-byte pieces: start of each pair's row area, pieces per contact
+  // 16-byte pieces: start of each pair's normal / friction block, pieces per contact there
+  int seg_lo[6], seg_per[6];
 #pragma unroll
   for (int m = 0; m < 3; ++m) {
+    const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
     seg_lo[m] = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4;
-    seg_per[m] = (L.rpc[m] * (m == BCP_PAIR_CART_POLE ? (int)SW2 : (int)SW1) * (int)sizeof(T)) >> 4;
+    seg_per[m] = (w * (int)sizeof(T)) >> 4;
+    seg_lo[3 + m] = L.fbase[m] >= 0 ? ((REC_ROWS + L.fbase[m]) * (int)sizeof(T)) >> 4 : rec16;
+    seg_per[3 + m] = ((L.rpc[m] - 1) * w * (int)sizeof(T)) >> 4;
   }
   int w_next = 0, w_end = 0;  // the warp's slice of the queue (uniform)
   bool exhausted = total == 0;
   SolveRegs<T> R;
-  solve_consts(P, R);
+  SolveScale<T> S;
+  solve_consts(P, R, S);
   int cnt[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
   int it = 0;
   T* rec = nullptr;
@@ -373,7 +380,7 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
       cp_async_wait_all();
       __syncwarp();
       if (staged) {
-        solve_load(col, cnt, R);
+        solve_load(col, S, cnt, R);
         it = 0;
         busy = true;
         staged = false;
@@ -418,7 +425,7 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
         for (int i = lane; i < rec16; i += 32) {
           bool live = i < hdr16;
 #pragma unroll
-          for (int m = 0; m < 3; ++m) live = live || (i >= seg_lo[m] && i - seg_lo[m] < ((m_src >> (8 * m)) & 0xff) * seg_per[m]);
+          for (int m = 0; m < 6; ++m) live = live || (i >= seg_lo[m] && i - seg_lo[m] < ((m_src >> (8 * (m % 3))) & 0xff) * seg_per[m]);
           cp_async16(c_dst + 16 * i, r_src + 16 * i, live ? 16 : 0);
         }
       }
@@ -427,7 +434,7 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
       if (!__any_sync(FULL, staged)) break;
       continue;
     }
-    const T lsr = solve_iteration<T, FRICTION>(P, col + REC_ROWS, L, mx, R);
+    const T lsr = solve_iteration<T, FRICTION, true>(P, col + REC_ROWS, L, mx, R);
     bool conv = false;
     if (busy) {
       it++;
@@ -435,7 +442,7 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
     }
     if (__any_sync(FULL, conv)) {
       if (conv) {  // retire at once: the lane keeps sweeping its stale column until it is refilled
-        solve_end(rec, cnt, it, R);
+        solve_end(rec, S, it, R);
         busy = false;
       }
 #pragma unroll

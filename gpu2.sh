@@ -1,7 +1,6 @@
 mkdir -p gpurun_out
+timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -4
 run() { timeout 600 python bench.py --steps 20 --warmup 3 --no-cpu-baseline $2 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', d['value'], d['kernel_ms_per_step'])"; }
-for n in 131072 262144; do run "envs $n" "--envs $n"; done
-for mb in 4 3 2; do
-  BCP_NVCC_EXTRA="-DBCP_PREP_MINB=$mb" python -c "from cartpoleplusplus_b200 import build; build.build(force=True)"
-  for pb in 128 64; do BCP_PREP_BLOCK=$pb run "minb $mb block $pb" ""; done
-done
+for c in 50 6 8 10 12 16; do BCP_SOLVE_CAP=$c run "cap $c" ""; done
+BCP_SOLVE_CAP=8 BCP_FETCH_MIN=4 run "cap 8 fm 4" ""
+BCP_SOLVE_CAP=8 BCP_FETCH_MIN=16 run "cap 8 fm 16" ""
