@@ -162,7 +162,8 @@ BCP_HD T cone_clip(T& apA, T& apB, T& dA, T& dB, T uA, T uB, T DA, T DB, T L) { 
   const T sumA = apA + dA, sumB = apB + dB;
   const T ss = sumA * sumA + sumB * sumB;
   const bool clip = ss >= L * L && ss > T(0.0);
-  const T sc = clip ? babs(L) * fast_rsqrt(ss) : T(1.0);
+  const T rs = babs(L) * fast_rsqrt(ss);  // issued without waiting for the clip decision
+  const T sc = clip ? rs : T(1.0);
   const T nA = sumA * sc, nB = sumB * sc;
   dA = nA - apA;
   dB = nB - apB;
@@ -235,6 +236,23 @@ BCP_HD T solve_iteration(const Params<T>& P, const T* colp, const SolveLayout& L
   load_row<SMEM>(gp, r_gp);
   load_row<SMEM>(cp, r_cp);
   load_row<SMEM>(gc, r_gc);
+  // first friction pair of every pair that has friction rows, also at the top
+  SRow1<T> f_gp_a, f_gp_b, f_gc_a, f_gc_b;
+  SRow2<T> f_cp_a, f_cp_b;
+  if (FRICTION) {
+    if (L.fbase[BCP_PAIR_GROUND_POLE] >= 0) {
+      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_POLE], f_gp_a);
+      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_POLE] + SW1, f_gp_b);
+    }
+    if (L.fbase[BCP_PAIR_CART_POLE] >= 0) {
+      load_row<SMEM>(colp + L.fbase[BCP_PAIR_CART_POLE], f_cp_a);
+      load_row<SMEM>(colp + L.fbase[BCP_PAIR_CART_POLE] + SW2, f_cp_b);
+    }
+    if (L.fbase[BCP_PAIR_GROUND_CART] >= 0) {
+      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_CART], f_gc_a);
+      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_CART] + SW1, f_gc_b);
+    }
+  }
 #pragma unroll
   for (int j = 0; j < 4; ++j) {
     if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
@@ -260,9 +278,7 @@ BCP_HD T solve_iteration(const Params<T>& P, const T* colp, const SolveLayout& L
     if (L.fbase[BCP_PAIR_GROUND_POLE] >= 0 && mx[BCP_PAIR_GROUND_POLE] > 0) {
       const T* row = colp + L.fbase[BCP_PAIR_GROUND_POLE];
       const T mu = P.mu[BCP_PAIR_GROUND_POLE];
-      SRow1<T> na, nb;
-      load_row<SMEM>(row, na);
-      load_row<SMEM>(row + SW1, nb);
+      SRow1<T> na = f_gp_a, nb = f_gp_b;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
@@ -274,9 +290,7 @@ BCP_HD T solve_iteration(const Params<T>& P, const T* colp, const SolveLayout& L
     if (L.fbase[BCP_PAIR_CART_POLE] >= 0 && mx[BCP_PAIR_CART_POLE] > 0) {
       const T* row = colp + L.fbase[BCP_PAIR_CART_POLE];
       const T mu = P.mu[BCP_PAIR_CART_POLE];
-      SRow2<T> na, nb;
-      load_row<SMEM>(row, na);
-      load_row<SMEM>(row + SW2, nb);
+      SRow2<T> na = f_cp_a, nb = f_cp_b;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         if (j >= mx[BCP_PAIR_CART_POLE]) break;
@@ -288,9 +302,7 @@ BCP_HD T solve_iteration(const Params<T>& P, const T* colp, const SolveLayout& L
     if (L.fbase[BCP_PAIR_GROUND_CART] >= 0 && mx[BCP_PAIR_GROUND_CART] > 0) {
       const T* row = colp + L.fbase[BCP_PAIR_GROUND_CART];
       const T mu = P.mu[BCP_PAIR_GROUND_CART];
-      SRow1<T> na, nb;
-      load_row<SMEM>(row, na);
-      load_row<SMEM>(row + SW1, nb);
+      SRow1<T> na = f_gc_a, nb = f_gc_b;
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         if (j >= mx[BCP_PAIR_GROUND_CART]) break;

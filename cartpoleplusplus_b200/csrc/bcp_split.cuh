@@ -343,6 +343,8 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src,
 }
 __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;\n" ::: "memory"); }
 
+constexpr int kMaxPieces = 4;  // 16-byte pieces of a record one lane copies (records <= 512 words)
+
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
                                                   const int2* __restrict__ queue, int* __restrict__ qc, int col_stride,
@@ -356,15 +358,24 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
   const int n_long = qc[Q_LONG], total = n_long + qc[Q_SHORT];
   const unsigned lt = (1u << lane) - 1;
   const int rec16 = (rec_words * (int)sizeof(T)) >> 4, hdr16 = (REC_ROWS * (int)sizeof(T)) >> 4;
-  // 16-byte pieces: start of each pair's normal / friction block, pieces per contact there
-  int seg_lo[6], seg_per[6];
+  // The record -> column copy: this lane moves the 16-byte pieces lane, lane + 32, ... of every
+  // record its warp takes.  What block a piece lies in never changes, so it is worked out once:
+  // piece k is live iff  pc_off[k] < count(pair pc_shift[k] / 8) * pc_per[k]   (header: always).
+  int pc_shift[kMaxPieces], pc_off[kMaxPieces], pc_per[kMaxPieces];
 #pragma unroll
-  for (int m = 0; m < 3; ++m) {
-    const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
-    seg_lo[m] = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4;
-    seg_per[m] = (w * (int)sizeof(T)) >> 4;
-    seg_lo[3 + m] = L.fbase[m] >= 0 ? ((REC_ROWS + L.fbase[m]) * (int)sizeof(T)) >> 4 : rec16;
-    seg_per[3 + m] = ((L.rpc[m] - 1) * w * (int)sizeof(T)) >> 4;
+  for (int k = 0; k < kMaxPieces; ++k) {
+    const int i = lane + 32 * k;
+    pc_shift[k] = 0; pc_off[k] = (i < hdr16) ? -1 : 0x7fffffff; pc_per[k] = 0;  // header piece / outside every block
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+      const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
+      const int lo = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4, per = (w * (int)sizeof(T)) >> 4;
+      if (i >= lo && i < lo + 4 * per) { pc_shift[k] = 8 * m; pc_off[k] = i - lo; pc_per[k] = per; }
+      if (L.fbase[m] >= 0) {
+        const int flo = ((REC_ROWS + L.fbase[m]) * (int)sizeof(T)) >> 4, fper = ((L.rpc[m] - 1) * w * (int)sizeof(T)) >> 4;
+        if (i >= flo && i < flo + 4 * fper) { pc_shift[k] = 8 * m; pc_off[k] = i - flo; pc_per[k] = fper; }
+      }
+    }
   }
   int w_next = 0, w_end = 0;  // the warp's slice of the queue (uniform)
   bool exhausted = total == 0;
@@ -374,21 +385,22 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
   int cnt[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
   int it = 0;
   T* rec = nullptr;
-  bool busy = false, staged = false;
+  unsigned busy_m = 0, staged_m = 0;  // lanes iterating / lanes whose copy is in flight (warp-uniform)
   while (true) {
-    if (__any_sync(FULL, staged)) {  // copies issued one iteration ago: start those lanes
+    if (staged_m) {  // copies issued one iteration ago: start those lanes
       cp_async_wait_all();
       __syncwarp();
-      if (staged) {
+      if ((staged_m >> lane) & 1u) {
         solve_load(col, S, cnt, R);
         it = 0;
-        busy = true;
-        staged = false;
       }
+      busy_m |= staged_m;
+      staged_m = 0;
+      const bool busy = (busy_m >> lane) & 1u;
 #pragma unroll
       for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
     }
-    const unsigned idle = __ballot_sync(FULL, !busy);
+    const unsigned idle = ~busy_m;
     if (idle && !exhausted && (idle == FULL || __popc(idle) >= fetch_min)) {
       unsigned need = idle;
       int idx = -1;
@@ -413,40 +425,42 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
         env = q.x;
         meta = q.y;
         rec = recs + (size_t)env * rec_words;
-        staged = true;
       }
-      unsigned taken = __ballot_sync(FULL, idx >= 0);
+      staged_m = __ballot_sync(FULL, idx >= 0);
+      unsigned taken = staged_m;
       while (taken) {
         const int src = __ffs(taken) - 1;
         taken &= taken - 1;
         const int e_src = __shfl_sync(FULL, env, src), m_src = __shfl_sync(FULL, meta, src);
-        const char* r_src = reinterpret_cast<const char*>(recs + (size_t)e_src * rec_words);
-        char* c_dst = reinterpret_cast<char*>(smem + (size_t)(warp_base + src) * col_stride);
-        for (int i = lane; i < rec16; i += 32) {
-          bool live = i < hdr16;
+        const char* r_src = reinterpret_cast<const char*>(recs + (size_t)e_src * rec_words) + 16 * lane;
+        char* c_dst = reinterpret_cast<char*>(smem + (size_t)(warp_base + src) * col_stride) + 16 * lane;
 #pragma unroll
-          for (int m = 0; m < 6; ++m) live = live || (i >= seg_lo[m] && i - seg_lo[m] < ((m_src >> (8 * (m % 3))) & 0xff) * seg_per[m]);
-          cp_async16(c_dst + 16 * i, r_src + 16 * i, live ? 16 : 0);
+        for (int k = 0; k < kMaxPieces; ++k) {
+          if (lane + 32 * k < rec16) {
+            const bool live = pc_off[k] < (int)((m_src >> pc_shift[k]) & 0xff) * pc_per[k];
+            cp_async16(c_dst + 512 * k, r_src + 512 * k, live ? 16 : 0);
+          }
         }
       }
     }
-    if (!__any_sync(FULL, busy)) {
-      if (!__any_sync(FULL, staged)) break;
+    if (!busy_m) {
+      if (!staged_m) break;
       continue;
     }
     const T lsr = solve_iteration<T, FRICTION, true>(P, col + REC_ROWS, L, mx, R);
+    const bool busy = (busy_m >> lane) & 1u;
     bool conv = false;
     if (busy) {
       it++;
       conv = lsr <= P.residual_thr || it >= P.solver_iterations;
     }
-    if (__any_sync(FULL, conv)) {
-      if (conv) {  // retire at once: the lane keeps sweeping its stale column until it is refilled
-        solve_end(rec, S, it, R);
-        busy = false;
-      }
+    const unsigned cm = __ballot_sync(FULL, conv);
+    if (cm) {
+      if (conv) solve_end(rec, S, it, R);  // retire at once: the lane sweeps its stale column until refilled
+      busy_m &= ~cm;
+      const bool still = (busy_m >> lane) & 1u;
 #pragma unroll
-      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
+      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, still ? cnt[m] : 0);
     }
   }
 }
