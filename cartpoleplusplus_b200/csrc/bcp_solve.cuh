@@ -228,90 +228,62 @@ BCP_HD T solve_iteration(const Params<T>& P, const T* colp, const SolveLayout& L
   T lsr = 0;
   const T cfm_n = P.cfm_normal, cfm_f = P.cfm_friction;
 #define BCP_ACC(r_) { const T r__ = (r_); const T r2__ = r__ * r__; lsr = (lsr > r2__) ? lsr : r2__; }
+// rows are swept two at a time between the warp-uniform exits (slots past a lane's count are zero
+// rows), through two register buffers used alternately: row j + 1 is in flight while row j runs
+#define BCP_SWEEP(PAIR, N_, LOAD_NEXT, SOLVE)             \
+  if (mx[PAIR] > 0) {                                      \
+    _Pragma("unroll") for (int j = 0; j < 4; ++j) {        \
+      if (j == 2 && mx[PAIR] <= 2) break;                  \
+      if (j < 3) { LOAD_NEXT; }                            \
+      BCP_ACC(SOLVE);                                      \
+    }                                                      \
+  }
   const T* const gp = colp + L.base[BCP_PAIR_GROUND_POLE];
   const T* const cp = colp + L.base[BCP_PAIR_CART_POLE];
   const T* const gc = colp + L.base[BCP_PAIR_GROUND_CART];
-  SRow1<T> r_gp, r_gc;
-  SRow2<T> r_cp;
-  load_row<SMEM>(gp, r_gp);
-  load_row<SMEM>(cp, r_cp);
-  load_row<SMEM>(gc, r_gc);
+  SRow1<T> r_gp[2], r_gc[2];
+  SRow2<T> r_cp[2];
+  load_row<SMEM>(gp, r_gp[0]);
+  load_row<SMEM>(cp, r_cp[0]);
+  load_row<SMEM>(gc, r_gc[0]);
   // first friction pair of every pair that has friction rows, also at the top
-  SRow1<T> f_gp_a, f_gp_b, f_gc_a, f_gc_b;
-  SRow2<T> f_cp_a, f_cp_b;
+  SRow1<T> f_gp[2][2], f_gc[2][2];
+  SRow2<T> f_cp[2][2];
+  const T* const fgp = colp + L.fbase[BCP_PAIR_GROUND_POLE];
+  const T* const fcp = colp + L.fbase[BCP_PAIR_CART_POLE];
+  const T* const fgc = colp + L.fbase[BCP_PAIR_GROUND_CART];
+  if (FRICTION) {
+    if (L.fbase[BCP_PAIR_GROUND_POLE] >= 0) { load_row<SMEM>(fgp, f_gp[0][0]); load_row<SMEM>(fgp + SW1, f_gp[0][1]); }
+    if (L.fbase[BCP_PAIR_CART_POLE] >= 0) { load_row<SMEM>(fcp, f_cp[0][0]); load_row<SMEM>(fcp + SW2, f_cp[0][1]); }
+    if (L.fbase[BCP_PAIR_GROUND_CART] >= 0) { load_row<SMEM>(fgc, f_gc[0][0]); load_row<SMEM>(fgc + SW1, f_gc[0][1]); }
+  }
+  BCP_SWEEP(BCP_PAIR_GROUND_POLE, 4, load_row<SMEM>(gp + (j + 1) * SW1, r_gp[(j + 1) & 1]),
+            solve_row1(r_gp[j & 1], R.pole, R.apn[SLOT_GP + j], cfm_n))
+  BCP_SWEEP(BCP_PAIR_CART_POLE, 4, load_row<SMEM>(cp + (j + 1) * SW2, r_cp[(j + 1) & 1]),
+            solve_row2(r_cp[j & 1], R.cart, R.pole, R.apn[SLOT_CP + j], cfm_n))
+  BCP_SWEEP(BCP_PAIR_GROUND_CART, 4, load_row<SMEM>(gc + (j + 1) * SW1, r_gc[(j + 1) & 1]),
+            solve_row1(r_gc[j & 1], R.cart, R.apn[SLOT_GC + j], cfm_n))
   if (FRICTION) {
     if (L.fbase[BCP_PAIR_GROUND_POLE] >= 0) {
-      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_POLE], f_gp_a);
-      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_POLE] + SW1, f_gp_b);
+      const T mu = P.mu[BCP_PAIR_GROUND_POLE];
+      BCP_SWEEP(BCP_PAIR_GROUND_POLE, 4,
+                load_row<SMEM>(fgp + (j + 1) * 2 * SW1, f_gp[(j + 1) & 1][0]); load_row<SMEM>(fgp + (j + 1) * 2 * SW1 + SW1, f_gp[(j + 1) & 1][1]),
+                solve_cone1(f_gp[j & 1][0], f_gp[j & 1][1], R.pole, R.apf[SLOT_GP + j][0], R.apf[SLOT_GP + j][1], mu * R.apn[SLOT_GP + j], cfm_f))
     }
     if (L.fbase[BCP_PAIR_CART_POLE] >= 0) {
-      load_row<SMEM>(colp + L.fbase[BCP_PAIR_CART_POLE], f_cp_a);
-      load_row<SMEM>(colp + L.fbase[BCP_PAIR_CART_POLE] + SW2, f_cp_b);
+      const T mu = P.mu[BCP_PAIR_CART_POLE];
+      BCP_SWEEP(BCP_PAIR_CART_POLE, 4,
+                load_row<SMEM>(fcp + (j + 1) * 2 * SW2, f_cp[(j + 1) & 1][0]); load_row<SMEM>(fcp + (j + 1) * 2 * SW2 + SW2, f_cp[(j + 1) & 1][1]),
+                solve_cone2(f_cp[j & 1][0], f_cp[j & 1][1], R.cart, R.pole, R.apf[SLOT_CP + j][0], R.apf[SLOT_CP + j][1], mu * R.apn[SLOT_CP + j], cfm_f))
     }
     if (L.fbase[BCP_PAIR_GROUND_CART] >= 0) {
-      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_CART], f_gc_a);
-      load_row<SMEM>(colp + L.fbase[BCP_PAIR_GROUND_CART] + SW1, f_gc_b);
-    }
-  }
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
-    const SRow1<T> cur = r_gp;
-    if (j < 3) load_row<SMEM>(gp + (j + 1) * SW1, r_gp);
-    BCP_ACC(solve_row1(cur, R.pole, R.apn[SLOT_GP + j], cfm_n));
-  }
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    if (j >= mx[BCP_PAIR_CART_POLE]) break;
-    const SRow2<T> cur = r_cp;
-    if (j < 3) load_row<SMEM>(cp + (j + 1) * SW2, r_cp);
-    BCP_ACC(solve_row2(cur, R.cart, R.pole, R.apn[SLOT_CP + j], cfm_n));
-  }
-#pragma unroll
-  for (int j = 0; j < 4; ++j) {
-    if (j >= mx[BCP_PAIR_GROUND_CART]) break;
-    const SRow1<T> cur = r_gc;
-    if (j < 3) load_row<SMEM>(gc + (j + 1) * SW1, r_gc);
-    BCP_ACC(solve_row1(cur, R.cart, R.apn[SLOT_GC + j], cfm_n));
-  }
-  if (FRICTION) {
-    if (L.fbase[BCP_PAIR_GROUND_POLE] >= 0 && mx[BCP_PAIR_GROUND_POLE] > 0) {
-      const T* row = colp + L.fbase[BCP_PAIR_GROUND_POLE];
-      const T mu = P.mu[BCP_PAIR_GROUND_POLE];
-      SRow1<T> na = f_gp_a, nb = f_gp_b;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (j >= mx[BCP_PAIR_GROUND_POLE]) break;
-        const SRow1<T> ca = na, cb = nb;
-        if (j < 3) { load_row<SMEM>(row + (j + 1) * 2 * SW1, na); load_row<SMEM>(row + (j + 1) * 2 * SW1 + SW1, nb); }
-        BCP_ACC(solve_cone1(ca, cb, R.pole, R.apf[SLOT_GP + j][0], R.apf[SLOT_GP + j][1], mu * R.apn[SLOT_GP + j], cfm_f));
-      }
-    }
-    if (L.fbase[BCP_PAIR_CART_POLE] >= 0 && mx[BCP_PAIR_CART_POLE] > 0) {
-      const T* row = colp + L.fbase[BCP_PAIR_CART_POLE];
-      const T mu = P.mu[BCP_PAIR_CART_POLE];
-      SRow2<T> na = f_cp_a, nb = f_cp_b;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (j >= mx[BCP_PAIR_CART_POLE]) break;
-        const SRow2<T> ca = na, cb = nb;
-        if (j < 3) { load_row<SMEM>(row + (j + 1) * 2 * SW2, na); load_row<SMEM>(row + (j + 1) * 2 * SW2 + SW2, nb); }
-        BCP_ACC(solve_cone2(ca, cb, R.cart, R.pole, R.apf[SLOT_CP + j][0], R.apf[SLOT_CP + j][1], mu * R.apn[SLOT_CP + j], cfm_f));
-      }
-    }
-    if (L.fbase[BCP_PAIR_GROUND_CART] >= 0 && mx[BCP_PAIR_GROUND_CART] > 0) {
-      const T* row = colp + L.fbase[BCP_PAIR_GROUND_CART];
       const T mu = P.mu[BCP_PAIR_GROUND_CART];
-      SRow1<T> na = f_gc_a, nb = f_gc_b;
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        if (j >= mx[BCP_PAIR_GROUND_CART]) break;
-        const SRow1<T> ca = na, cb = nb;
-        if (j < 3) { load_row<SMEM>(row + (j + 1) * 2 * SW1, na); load_row<SMEM>(row + (j + 1) * 2 * SW1 + SW1, nb); }
-        BCP_ACC(solve_cone1(ca, cb, R.cart, R.apf[SLOT_GC + j][0], R.apf[SLOT_GC + j][1], mu * R.apn[SLOT_GC + j], cfm_f));
-      }
+      BCP_SWEEP(BCP_PAIR_GROUND_CART, 4,
+                load_row<SMEM>(fgc + (j + 1) * 2 * SW1, f_gc[(j + 1) & 1][0]); load_row<SMEM>(fgc + (j + 1) * 2 * SW1 + SW1, f_gc[(j + 1) & 1][1]),
+                solve_cone1(f_gc[j & 1][0], f_gc[j & 1][1], R.cart, R.apf[SLOT_GC + j][0], R.apf[SLOT_GC + j][1], mu * R.apn[SLOT_GC + j], cfm_f))
     }
   }
+#undef BCP_SWEEP
 #undef BCP_ACC
   return lsr;
 }

@@ -386,6 +386,8 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
   int it = 0;
   T* rec = nullptr;
   unsigned busy_m = 0, staged_m = 0;  // lanes iterating / lanes whose copy is in flight (warp-uniform)
+  const T res_thr = P.residual_thr;
+  const int max_it = P.solver_iterations;
   while (true) {
     if (staged_m) {  // copies issued one iteration ago: start those lanes
       cp_async_wait_all();
@@ -452,7 +454,7 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
     bool conv = false;
     if (busy) {
       it++;
-      conv = lsr <= P.residual_thr || it >= P.solver_iterations;
+      conv = lsr <= res_thr || it >= max_it;
     }
     const unsigned cm = __ballot_sync(FULL, conv);
     if (cm) {
