@@ -61,14 +61,30 @@ def solve_flops(info, cfg):
     return it * per_iter
 
 
-def solve_bytes(info, cfg):
-    """Algorithmic bytes one solve moves per env: the live rows of its record in, the
-    velocity deltas, iteration count and normal impulses out (fp32)."""
+def _row_words(info, cfg):
     gc, cp, gp = (info[:, 3 + k].astype(np.float64) for k in range(3))
     rpc = lambda a, b: 3 if (a * b) and cfg.friction_dirs == 2 else 1  # noqa: E731
-    words = (gc * rpc(cfg.ground.friction, cfg.cart.friction) * 10 + gp * rpc(cfg.ground.friction, cfg.pole.friction) * 10
-             + cp * rpc(cfg.cart.friction, cfg.pole.friction) * 13)
-    return 4.0 * (words + 16 + 13 + (gc + cp + gp))
+    return (gc * rpc(cfg.ground.friction, cfg.cart.friction) * 8 + gp * rpc(cfg.ground.friction, cfg.pole.friction) * 8
+            + cp * rpc(cfg.cart.friction, cfg.pole.friction) * 12)
+
+
+def solve_bytes(info, cfg):
+    """Algorithmic bytes k_solve moves per env (fp32): the record header (32 words) and its live
+    rows (8 / 12 words per one- / two-body row) in; iteration count, velocity deltas and normal
+    impulses (25 words) out."""
+    return 4.0 * (32 + _row_words(info, cfg) + 25)
+
+
+def prep_bytes(info, cfg, RS):
+    """Algorithmic bytes k_prep moves per env and launch, averaged over the RS + 1 launches of a
+    call: the env record (164 floats + 8 ints) in and out every launch; RS of them write a solve
+    record (header + live rows) and RS read one back (header) and the action; the last writes the
+    (R,2,7) observation, reward, done and reason."""
+    state = 2.0 * (164 * 4 + 8 * 4)
+    setup = 4.0 * (32 + _row_words(info, cfg))
+    finish = 4.0 * 32 + 8.0
+    close = cfg.action_repeats * 14 * 4 + 6.0
+    return state + (RS * (setup + finish) + close) / (RS + 1)
 
 
 # ---------------------------------------------------------------------------------------
@@ -251,23 +267,45 @@ def run_ours(args):
     flops_env = float(solve_flops(info, env.cfg).mean())
     bytes_env = float(solve_bytes(info, env.cfg).mean())
     split = prof["n_solve"] > 0
-    dom_name = "k_solve" if split else "k_step"
-    dom_ms = (prof["ms_solve"] / max(1, prof["n_solve"])) if split else (prof["ms_prep"] / max(1, prof["n_prep"]))
-    flops_launch = flops_env * n * (1 if split else RS)
-    bytes_launch = bytes_env * n * (1 if split else RS)
     lib = _lib.load()
     peak32, peak64 = ctypes.c_double(), ctypes.c_double()
     lib.bcp_bench_fma_peak(local, 0, 4096, ctypes.byref(peak32))
     lib.bcp_bench_fma_peak(local, 1, 1024, ctypes.byref(peak64))
     pipe_peak = peak64.value if args.dtype == "fp64" else peak32.value
-    achieved_tf = flops_launch / (dom_ms * 1e-3) / 1e12
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
     except Exception:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    achieved_gbs = bytes_launch / (dom_ms * 1e-3) / 1e9
+    traffic = {}
+    try:  # dram__bytes_read.sum + dram__bytes_write.sum per launch, from the committed ncu --set full captures
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+    except Exception:
+        pass
+    # per kernel: algorithmic bytes of one launch / its average launch time in the timed region
+    kernels = {}
+    if split:
+        pb = float(prep_bytes(info, env.cfg, RS).mean())
+        kernels["k_prep"] = {"ms_per_step": prof["ms_prep"] / K, "launch_ms": prof["ms_prep"] / max(1, prof["n_prep"]),
+                             "bytes_per_env_launch": pb, "bytes_per_launch": pb * n}
+        kernels["k_solve"] = {"ms_per_step": prof["ms_solve"] / K, "launch_ms": prof["ms_solve"] / max(1, prof["n_solve"]),
+                              "bytes_per_env_launch": bytes_env, "bytes_per_launch": bytes_env * n}
+    else:
+        kernels["k_step"] = {"ms_per_step": prof["ms_prep"] / K, "launch_ms": prof["ms_prep"] / max(1, prof["n_prep"]),
+                             "bytes_per_env_launch": 2.0 * 176 * 8 + 8, "bytes_per_launch": (2.0 * 176 * 8 + 8) * n}
+    for name, kd in kernels.items():
+        kd["achieved_gbs"] = kd["bytes_per_launch"] / (kd["launch_ms"] * 1e-3) / 1e9
+        kd["frac_of_hbm_peak"] = kd["achieved_gbs"] / hbm_peak
+        kd["share_of_step"] = kd["ms_per_step"] * K / total_ms
+        t = traffic.get(name if args.dtype == "fp32" else name + "_f64")
+        kd["traffic"] = t.get("bytes_per_launch") if isinstance(t, dict) and int(t.get("num_envs", n)) == n else None
+    dom_name = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
+    dom = kernels[dom_name]
+    solve_name = "k_solve" if split else "k_step"
+    solve_ms = kernels[solve_name]["launch_ms"]
+    flops_launch = flops_env * n * (1 if split else RS)
+    achieved_tf = flops_launch / (solve_ms * 1e-3) / 1e12
     value = live_all / (total_ms * 1e-3)
     out = {
         "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -287,16 +325,22 @@ def run_ours(args):
         "substeps_per_s": world * n * K * RS / (total_ms * 1e-3),
         "episodes_finished": episodes_all,
         "mean_episode_len": float((hist_t.cpu().numpy() * np.arange(len(hist))).sum() / max(1, int(hist_t.sum().item()))),
-        "kernel_ms_per_step": {"k_prep" if split else "k_step": prof["ms_prep"] / K, "k_solve": prof["ms_solve"] / K},
+        "kernel_ms_per_step": {k: v["ms_per_step"] for k, v in kernels.items()},
         "e2e": {"value": e2e_live_all / (e2e_ms * 1e-3), "unit": "env-steps/s",
                 "h2d_bytes_per_step": env.h2d_bytes_per_step, "d2h_bytes_per_step": env.d2h_bytes_per_step},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
-        "roofline": {"bound": "hbm", "achieved": achieved_gbs, "peak": hbm_peak, "unit": "GB/s",
-                     "frac": achieved_gbs / hbm_peak, "traffic": None, "kernel": dom_name,
-                     "note": "schema-mandated HBM view; the kernel is FP32-pipe / issue-latency bound, see roofline_pipe"},
-        "roofline_pipe": {"bound": "fp32-cuda-core" if args.dtype == "fp32" else "fp64-cuda-core", "kernel": dom_name,
-                          "launch_ms": dom_ms, "share_of_step": (prof["ms_solve"] if split else prof["ms_prep"]) / total_ms,
+        # the dominant kernel (largest share of the step) against the measured HBM copy bandwidth
+        "roofline": {"bound": "hbm", "achieved": dom["achieved_gbs"], "peak": hbm_peak, "unit": "GB/s",
+                     "frac": dom["frac_of_hbm_peak"], "traffic": dom["traffic"], "kernel": dom_name,
+                     "launch_ms": dom["launch_ms"], "share_of_step": dom["share_of_step"],
+                     "algorithmic_bytes_per_env_launch": dom["bytes_per_env_launch"],
+                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
+                     "note": "both kernels are issue-latency bound, not bandwidth bound (profiles/); "
+                             "see roofline_kernels and roofline_pipe"},
+        "roofline_kernels": kernels,
+        "roofline_pipe": {"bound": "fp32-cuda-core" if args.dtype == "fp32" else "fp64-cuda-core", "kernel": solve_name,
+                          "launch_ms": solve_ms, "share_of_step": kernels[solve_name]["share_of_step"],
                           "achieved": achieved_tf, "peak": pipe_peak, "unit": "TFLOP/s", "frac": achieved_tf / pipe_peak,
                           "peak_source": "bcp_bench_fma_peak (FMA chains, measured in this run)",
                           "flops_per_env_solve": flops_env, "bytes_per_env_solve": bytes_env,
