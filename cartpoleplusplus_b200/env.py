@@ -46,10 +46,15 @@ class BatchedBulletCartpole:
         _lib.check(self._lib.bcp_create(ctypes.byref(self.cfg), ctypes.byref(h)), self._lib)
         self._h = h
         n, dev = self.num_envs, self.device
-        self.obs = torch.zeros((n, self.repeats, 2, 7), dtype=torch.float32, device=dev)
-        self.reward = torch.zeros(n, dtype=torch.float32, device=dev)
-        self.done = torch.ones(n, dtype=torch.uint8, device=dev)  # no state until reset (:147-148)
-        self.reason = torch.zeros(n, dtype=torch.uint8, device=dev)
+        # the four outputs of a call are views of ONE device buffer, so that a host-side caller
+        # fetches them with a single device->host copy (step_host)
+        ob, rb = n * self.repeats * 14 * 4, n * 4
+        self._out = torch.zeros(ob + rb + 2 * n, dtype=torch.uint8, device=dev)
+        self.obs = self._out[:ob].view(torch.float32).view(n, self.repeats, 2, 7)
+        self.reward = self._out[ob:ob + rb].view(torch.float32)
+        self.done = self._out[ob + rb:ob + rb + n]
+        self.done.fill_(1)  # no state until reset (:147-148)
+        self.reason = self._out[ob + rb + n:]
         self._was_reset = False
 
     # ---- gym no-ops, bullet_cartpole.py:169-176 ----
@@ -124,25 +129,26 @@ class BatchedBulletCartpole:
         info = {"done_reason": self.reason.clone() if copy else self.reason}
         if copy:
             return self.obs.clone(), self.reward.clone(), self.done.bool(), info
-        return self.obs, self.reward, self.done.bool(), info
+        return self.obs, self.reward, self.done.view(torch.bool), info  # 0/1 bytes: a view, no kernel
 
     # ---- host-buffer call: what a CPU-side agent loop uses (pinned buffers, one sync) ----
     def step_host(self, actions_host: torch.Tensor, auto_reset: bool = False):
         """env.step with HOST tensors: H2D of the actions, the step kernel, (optionally) the
         reset of finished envs, D2H of obs/reward/done into pinned buffers, one stream sync.
         Returns pinned CPU tensors (overwritten by the next call)."""
-        if not hasattr(self, "_h_obs"):
-            self._h_obs = torch.empty(self.obs.shape, dtype=torch.float32).pin_memory()
-            self._h_reward = torch.empty(self.num_envs, dtype=torch.float32).pin_memory()
-            self._h_done = torch.empty(self.num_envs, dtype=torch.uint8).pin_memory()
+        if not hasattr(self, "_h_out"):
+            n, ob, rb = self.num_envs, self.obs.numel() * 4, self.num_envs * 4
+            self._h_out = torch.empty(self._out.numel(), dtype=torch.uint8).pin_memory()
+            self._h_obs = self._h_out[:ob].view(torch.float32).view(self.obs.shape)
+            self._h_reward = self._h_out[ob:ob + rb].view(torch.float32)
+            self._h_done = self._h_out[ob + rb:ob + rb + n]
+            self._h_reason = self._h_out[ob + rb + n:]
             adt = torch.int32 if self.discrete_actions else torch.float32
             ashape = (self.num_envs,) if self.discrete_actions else (self.num_envs, 2)
             self._d_act = torch.empty(ashape, dtype=adt, device=self.device)
         self._d_act.copy_(actions_host.reshape(self._d_act.shape), non_blocking=True)
-        obs, reward, done, _ = self.step(self._d_act, copy=False)
-        self._h_obs.copy_(obs, non_blocking=True)
-        self._h_reward.copy_(reward, non_blocking=True)
-        self._h_done.copy_(self.done, non_blocking=True)
+        self.step(self._d_act, copy=False)
+        self._h_out.copy_(self._out, non_blocking=True)  # obs, reward, done, reason in one transfer
         if auto_reset:  # the next observation of a finished env is its reset observation
             self.reset(mask=self.done, copy=False)
         torch.cuda.current_stream(self.device).synchronize()
@@ -154,7 +160,7 @@ class BatchedBulletCartpole:
 
     @property
     def d2h_bytes_per_step(self) -> int:
-        return self.num_envs * (self.repeats * 14 * 4 + 4 + 1)
+        return self.num_envs * (self.repeats * 14 * 4 + 4 + 1 + 1)
 
     # ---- device-side random-agent protocol (README.md:76-93) ----
     def rollout_random(self, n_calls: int, actions=(0, 1, 2, 3, 4), max_episodes: int = 0):
