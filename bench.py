@@ -95,6 +95,8 @@ def cpu_rollout(args, n_envs, n_steps, warm_steps):
     (+ the 130-substep resets they trigger), OpenMP over all host threads.  Same workload,
     same action distribution, from the stationary phase mix."""
     from oracle import Oracle
+    from oracle.oracle import set_threads
+    set_threads(os.cpu_count() or 1)  # torchrun exports OMP_NUM_THREADS=1; the baseline uses every host thread
     cfg = make_config(workload_opts(args), False, num_envs=n_envs, dtype="fp64", seed=args.seed)
     ora = Oracle(cfg, dtype="fp64")
     ora.state[:, C.S_DONE] = 1  # rollout_random resets every env first

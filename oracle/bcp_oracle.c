@@ -1313,6 +1313,21 @@ static void draw_action(const bcp_config* cfg, int64_t global_env, const ostate*
 /* ======================================================================== */
 /* exported entry points (ctypes; numpy buffers)                              */
 /* ======================================================================== */
+#if defined(_OPENMP)
+#include <omp.h>
+#endif
+/* threads of the parallel loops below; <= 0: leave the OpenMP default (launchers such as
+ * torchrun export OMP_NUM_THREADS=1, which would silently serialise the CPU baseline) */
+int SFX(bcpo_set_threads)(int n) {
+#if defined(_OPENMP)
+  if (n > 0) omp_set_num_threads(n);
+  return omp_get_max_threads();
+#else
+  (void)n;
+  return 1;
+#endif
+}
+
 int SFX(bcpo_substep)(const bcp_config* cfg, double* state, int n_envs, int32_t* info_out /*[n][6] or NULL*/) {
   int e;
 #pragma omp parallel for schedule(static)

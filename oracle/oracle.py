@@ -48,6 +48,14 @@ def _ptr(a, ctype):
     return a.ctypes.data_as(ctypes.POINTER(ctype)) if a is not None else None
 
 
+def set_threads(n: int) -> int:
+    """OpenMP threads of the oracle's batch loops (the library's own setting: OMP_NUM_THREADS of
+    the launcher does not apply afterwards).  Returns the thread count in effect."""
+    lib = _lib()
+    lib.bcpo_set_threads_f32(int(n))
+    return int(lib.bcpo_set_threads_f64(int(n)))
+
+
 class Oracle:
     """Batched CPU oracle over canonical state records (n, STATE_DOUBLES) float64."""
 
