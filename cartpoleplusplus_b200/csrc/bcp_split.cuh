@@ -49,56 +49,63 @@ BCP_HD int slot_of_pair(int m) { return m == BCP_PAIR_GROUND_CART ? (int)SLOT_GC
 
 // setup half of a substep for one env: rows + header into `rec`, the unconstrained
 // velocities parked in the state (angular in the BODY frame until split_finish).
-template <typename T, bool FRICTION>
-BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
+// The setup in pieces, so that k_prep can stream the manifolds through it one pair at a time:
+// setup_begin (poses, forward dynamics), setup_pair x 3 (narrowphase, manifold cache, rows),
+// setup_end (record header, velocities parked in the state).
+template <typename T> struct SetupCtx {
   Posed<T> gbox, cbox, pbox;
   FBody<T> cart, pole;
-  const SolveLayout L = solve_layout(P);
-  BCP_WARP_SYNC();
-  if (on) {
-    for (int i = 0; i < 3; ++i) { gbox.x[i] = P.ground.x0[i]; gbox.h[i] = P.ground.h[i]; }
-    for (int i = 0; i < 9; ++i) gbox.R[i] = (i % 4 == 0) ? T(1.0) : T(0.0);
-    pose_box(st.cart, P.cart, cbox);
-    pose_box(st.pole, P.pole, pbox);
-    const T zero3[3] = {0, 0, 0};
-    fbody_begin(P, st.cart, P.cart, cbox.R, st.pend_f, st.pend_t, cart);
-    fbody_begin(P, st.pole, P.pole, pbox.R, zero3, zero3, pole);
-  }
   T apn_all[N_SLOTS];
-  for (int k = 0; k < N_SLOTS; ++k) apn_all[k] = T(0.0);
-  for (int m = 0; m < 3; ++m) {
-    BCP_WARP_SYNC();
-    if (on) {
-      const Posed<T>& A = (m == BCP_PAIR_CART_POLE) ? cbox : gbox;
-      const Posed<T>& B = (m == BCP_PAIR_GROUND_CART) ? cbox : pbox;
-      Contact<T> cs[4];
-      WorldPt<T> wp[4];
-      const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, cs);
-      for (int k = 0; k < nc; ++k) manifold_add(st.mani[m], A, B, cs[k], P.breaking[m]);
-      manifold_refresh(st.mani[m], A, B, P.breaking[m], wp);
-      T* rows = rec + REC_ROWS + L.base[m];
-      T* frows = rec + REC_ROWS + (L.fbase[m] >= 0 ? L.fbase[m] : 0);
-      T* apn = apn_all + slot_of_pair(m);
-      if (m == BCP_PAIR_GROUND_CART) put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], st.mani[m], wp, cart, cart);
-      else if (m == BCP_PAIR_CART_POLE) put_rows<T, FRICTION, true>(P, rows, frows, apn, m, L.rpc[m], st.mani[m], wp, cart, pole);
-      else put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], st.mani[m], wp, pole, pole);
-    }
+};
+template <typename T> BCP_HD void setup_begin(const Params<T>& P, const Env<T>& st, SetupCtx<T>& C) {
+  for (int i = 0; i < 3; ++i) { C.gbox.x[i] = P.ground.x0[i]; C.gbox.h[i] = P.ground.h[i]; }
+  for (int i = 0; i < 9; ++i) C.gbox.R[i] = (i % 4 == 0) ? T(1.0) : T(0.0);
+  pose_box(st.cart, P.cart, C.cbox);
+  pose_box(st.pole, P.pole, C.pbox);
+  const T zero3[3] = {0, 0, 0};
+  fbody_begin(P, st.cart, P.cart, C.cbox.R, st.pend_f, st.pend_t, C.cart);
+  fbody_begin(P, st.pole, P.pole, C.pbox.R, zero3, zero3, C.pole);
+  for (int k = 0; k < N_SLOTS; ++k) C.apn_all[k] = T(0.0);
+}
+template <typename T, bool FRICTION>
+BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, SetupCtx<T>& C, T* rec, const SolveLayout& L) {
+  const Posed<T>& A = (m == BCP_PAIR_CART_POLE) ? C.cbox : C.gbox;
+  const Posed<T>& B = (m == BCP_PAIR_GROUND_CART) ? C.cbox : C.pbox;
+  Contact<T> cs[4];
+  WorldPt<T> wp[4];
+  const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, cs);
+  for (int k = 0; k < nc; ++k) manifold_add(mf, A, B, cs[k], P.breaking[m]);
+  manifold_refresh(mf, A, B, P.breaking[m], wp);
+  T* rows = rec + REC_ROWS + L.base[m];
+  T* frows = rec + REC_ROWS + (L.fbase[m] >= 0 ? L.fbase[m] : 0);
+  T* apn = C.apn_all + slot_of_pair(m);
+  if (m == BCP_PAIR_GROUND_CART) put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, C.cart, C.cart);
+  else if (m == BCP_PAIR_CART_POLE) put_rows<T, FRICTION, true>(P, rows, frows, apn, m, L.rpc[m], mf, wp, C.cart, C.pole);
+  else put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, C.pole, C.pole);
+}
+template <typename T> BCP_HD void setup_end(const Params<T>& P, Env<T>& st, const SetupCtx<T>& C, T* rec) {
+  rec[REC_C_GC] = as_real(st.mani[BCP_PAIR_GROUND_CART].count, T(0));
+  rec[REC_C_CP] = as_real(st.mani[BCP_PAIR_CART_POLE].count, T(0));
+  rec[REC_C_GP] = as_real(st.mani[BCP_PAIR_GROUND_POLE].count, T(0));
+  T d[12];
+  for (int i = 0; i < 3; ++i) {  // warm-start deltas
+    d[i] = C.cart.dwl[i]; d[3 + i] = C.cart.dv[i];
+    d[6 + i] = C.pole.dwl[i]; d[9 + i] = C.pole.dv[i];
+    st.cart.w[i] = C.cart.wl[i]; st.cart.v[i] = C.cart.v[i];
+    st.pole.w[i] = C.pole.wl[i]; st.pole.v[i] = C.pole.v[i];
+    st.pend_f[i] = 0; st.pend_t[i] = 0;  // clearForcesAndTorques
   }
-  BCP_WARP_SYNC();
-  if (on) {
-    rec[REC_C_GC] = as_real(st.mani[BCP_PAIR_GROUND_CART].count, T(0));
-    rec[REC_C_CP] = as_real(st.mani[BCP_PAIR_CART_POLE].count, T(0));
-    rec[REC_C_GP] = as_real(st.mani[BCP_PAIR_GROUND_POLE].count, T(0));
-    T d[12];
-    for (int i = 0; i < 3; ++i) {  // warm-start deltas
-      d[i] = cart.dwl[i]; d[3 + i] = cart.dv[i];
-      d[6 + i] = pole.dwl[i]; d[9 + i] = pole.dv[i];
-      st.cart.w[i] = cart.wl[i]; st.cart.v[i] = cart.v[i];
-      st.pole.w[i] = pole.wl[i]; st.pole.v[i] = pole.v[i];
-      st.pend_f[i] = 0; st.pend_t[i] = 0;  // clearForcesAndTorques
-    }
-    for (int k = 0; k < 3; ++k) { st4(rec + REC_DVEL + 4 * k, d + 4 * k); st4(rec + REC_APN + 4 * k, apn_all + 4 * k); }
-  }
+  for (int k = 0; k < 3; ++k) { st4(rec + REC_DVEL + 4 * k, d + 4 * k); st4(rec + REC_APN + 4 * k, C.apn_all + 4 * k); }
+}
+// the whole setup on a fully loaded env (host composition below, tests)
+template <typename T, bool FRICTION>
+BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
+  if (!on) return;
+  SetupCtx<T> C;
+  const SolveLayout L = solve_layout(P);
+  setup_begin(P, st, C);
+  for (int m = 0; m < 3; ++m) setup_pair<T, FRICTION>(P, m, st.mani[m], C, rec, L);
+  setup_end(P, st, C, rec);
 }
 
 // what a lane needs to start a solve: contact counts, warm-start deltas and impulses
@@ -143,8 +150,9 @@ template <typename T> BCP_HD void solve_end(T* rec, const SolveScale<T>& S, int 
   for (int k = 0; k < 3; ++k) { st4(rec + REC_DVEL + 4 * k, d + 4 * k); st4(rec + REC_APN + 4 * k, R.apn + 4 * k); }
 }
 
-// finish half of a substep: velocities += deltas, integrate, impulses -> manifold cache
-template <typename T> BCP_HD void split_finish(const Params<T>& P, Env<T>& st, const T* rec) {
+// finish half of a substep: velocities += deltas, integrate (finish_bodies), impulses ->
+// manifold cache (split_finish adds that for a fully loaded env; k_prep does it per pair)
+template <typename T> BCP_HD void finish_bodies(const Params<T>& P, Env<T>& st, const T* rec) {
   FBody<T> cart, pole;
   for (int i = 0; i < 3; ++i) {
     cart.dwl[i] = rec[REC_DVEL + i]; cart.dv[i] = rec[REC_DVEL + 3 + i];
@@ -154,10 +162,13 @@ template <typename T> BCP_HD void split_finish(const Params<T>& P, Env<T>& st, c
   }
   quat_to_mat(st.cart.q, cart.R);
   quat_to_mat(st.pole.q, pole.R);
-  for (int m = 0; m < 3; ++m)
-    for (int j = 0; j < st.mani[m].count; ++j) st.mani[m].p[j].imp = rec[REC_APN + slot_of_pair(m) + j];
   fbody_finish(P, cart, st.cart);
   fbody_finish(P, pole, st.pole);
+}
+template <typename T> BCP_HD void split_finish(const Params<T>& P, Env<T>& st, const T* rec) {
+  for (int m = 0; m < 3; ++m)
+    for (int j = 0; j < st.mani[m].count; ++j) st.mani[m].p[j].imp = rec[REC_APN + slot_of_pair(m) + j];
+  finish_bodies(P, st, rec);
 }
 
 // host-side composition (tests): the whole substep through a record, one env.  Slots the env
@@ -225,6 +236,13 @@ __device__ __forceinline__ int visit(const VisitOrder& vo, int i, int N) {
   return -1;
 }
 
+// a finished solve's normal impulses into the cached points of pair m, in place in the record
+// (the only thing a finish changes in a manifold)
+template <typename T> BCP_HD void finish_impulses(T* f, size_t e, int m, int count, const T* fin_apn) {
+  T* blk = f + e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE;
+  for (int j = 0; j < 4; ++j)
+    if (j < count) blk[j * BCP_MANI_POINT + 10] = fin_apn[slot_of_pair(m) + j];
+}
 template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
   return st.mani[0].count | (st.mani[1].count << 8) | (st.mani[2].count << 16);
 }
@@ -250,13 +268,19 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   st.done = 1;
   st.reset_left = 0;
   int mode = MODE_IDLE;
+  for (int m = 0; m < 3; ++m) st.mani[m].count = 0;
   if (valid) {
-    load_env<T>(f, id, N, e, st);
+    load_env_core<T>(f, id, e, st);  // the manifold points are streamed per pair below
     mode = id[(size_t)e * NI + I_MODE];
   }
   if (s_fin < 0) mode = call_begin(P, st, valid);
+  const bool fin = s_fin >= 0 && valid && substep_on(mode, st);
+  T fin_apn[N_SLOTS];  // applied normal impulses of the solve being finished -> manifold caches
+  if (fin) {
+    for (int k = 0; k < 3; ++k) ld4(rec + REC_APN + 4 * k, fin_apn + 4 * k);
+    finish_bodies(P, st, rec);
+  }
   if (s_fin >= 0 && valid) {
-    if (substep_on(mode, st)) split_finish(P, st, rec);
     int a = 0;
     float ax = 0.f, ay = 0.f;
     if (mode == MODE_LIVE) {
@@ -274,7 +298,27 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   if (s_set >= 0) {
     const bool on = valid && substep_on(mode, st);
     const int last_iters = on ? as_int(rec[REC_ITERS]) : 0;
-    split_setup<T, FRICTION>(P, st, rec, on);
+    SetupCtx<T> C;
+    const SolveLayout L = solve_layout(P);
+    BCP_WARP_SYNC();
+    if (on) setup_begin(P, st, C);
+#pragma unroll 1
+    for (int m = 0; m < 3; ++m) {
+      BCP_WARP_SYNC();
+      if (on) {
+        Manifold<T> mf;
+        mf.count = st.mani[m].count;
+        load_manifold<T>(f, e, m, mf);
+        if (fin) for (int j = 0; j < mf.count; ++j) mf.p[j].imp = fin_apn[slot_of_pair(m) + j];
+        setup_pair<T, FRICTION>(P, m, mf, C, rec, L);
+        st.mani[m].count = mf.count;
+        store_manifold<T>(f, e, m, mf);
+      } else if (fin) {
+        finish_impulses(f, e, m, st.mani[m].count, fin_apn);
+      }
+    }
+    BCP_WARP_SYNC();
+    if (on) setup_end(P, st, C, rec);
     // queue the env: one atomic per warp and bin
     const bool is_long = on && last_iters >= kLongIters;
     const unsigned ml = __ballot_sync(0xffffffffu, is_long), ms = __ballot_sync(0xffffffffu, on && !is_long);
@@ -292,6 +336,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     if (is_long) queue[bl + __popc(ml & lt)] = entry;
     else if (on) queue[N - 1 - (bs + __popc(ms & lt))] = entry;
   } else {  // the call closes: steps / done / reward (:239-260), outputs, episode statistics
+    if (fin) for (int m = 0; m < 3; ++m) finish_impulses(f, e, m, st.mani[m].count, fin_apn);
     bool live = false;
     const int rs = call_end(P, st, mode, obs, live);
     if (valid) {
@@ -323,7 +368,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     }
   }
   if (valid) {
-    store_env<T>(f, id, N, e, st);
+    store_env_core<T>(f, id, e, st);
     id[(size_t)e * NI + I_MODE] = mode;
   }
 }

@@ -60,10 +60,11 @@ template <typename T> BCP_HD void pack_body(const Body<T>& o, T* b) {
   for (int i = 0; i < 4; ++i) b[3 + i] = o.q[i];
 }
 
-// `N` is unused (kept so that call sites read the same for any layout)
-template <typename T>
-BCP_HD void load_env(const T* __restrict__ f, const int* __restrict__ id, size_t N, size_t e, Env<T>& st) {
-  (void)N;
+// A record is read and written in pieces: the CORE (bodies, pending force, counters, the three
+// point counts) and, separately, the point block of each manifold - the split pipeline streams
+// a pair's points in right before it works on the pair and out right after (short reuse
+// distance in L1), and leaves the blocks it does not touch where they are.
+template <typename T> BCP_HD void load_env_core(const T* f, const int* id, size_t e, Env<T>& st) {
   const T* r = f + e * NF;
   const int* ir = id + e * NI;
   int iv[NI];
@@ -80,30 +81,41 @@ BCP_HD void load_env(const T* __restrict__ f, const int* __restrict__ id, size_t
   unpack_body(head + BCP_S_CART, st.cart);
   unpack_body(head + BCP_S_POLE, st.pole);
   for (int i = 0; i < 3; ++i) { st.pend_f[i] = head[BCP_S_PEND_F + i]; st.pend_t[i] = head[BCP_S_PEND_T + i]; }
-  for (int m = 0; m < 3; ++m) {
-    st.mani[m].count = iv[I_CNT + m];
-    if (st.mani[m].count > 0) {
-      T blk[BCP_MANI_STRIDE];
-      copy16(r + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
-      for (int k = 0; k < 4; ++k) {
-        if (k < st.mani[m].count) {
-          const T* q = blk + k * BCP_MANI_POINT;
-          MPoint<T>& p = st.mani[m].p[k];
-          for (int i = 0; i < 3; ++i) { p.la[i] = q[i]; p.lb[i] = q[3 + i]; p.n[i] = q[6 + i]; }
-          p.dist = q[9];
-          p.imp = q[10];
-        }
-      }
-    }
-  }
+  for (int m = 0; m < 3; ++m) st.mani[m].count = iv[I_CNT + m];
   st.steps = iv[I_STEPS];
   st.done = iv[I_DONE];
   st.episode = iv[I_EPISODE];
   st.reset_left = iv[I_RESET_LEFT];
 }
-template <typename T>
-BCP_HD void store_env(T* __restrict__ f, int* __restrict__ id, size_t N, size_t e, const Env<T>& st) {
-  (void)N;
+// points 0..mf.count-1 of pair m (mf.count is set by the caller)
+template <typename T> BCP_HD void load_manifold(const T* f, size_t e, int m, Manifold<T>& mf) {
+  if (mf.count <= 0) return;
+  T blk[BCP_MANI_STRIDE];
+  copy16(f + e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
+  for (int k = 0; k < 4; ++k) {
+    if (k < mf.count) {
+      const T* q = blk + k * BCP_MANI_POINT;
+      MPoint<T>& p = mf.p[k];
+      for (int i = 0; i < 3; ++i) { p.la[i] = q[i]; p.lb[i] = q[3 + i]; p.n[i] = q[6 + i]; }
+      p.dist = q[9];
+      p.imp = q[10];
+    }
+  }
+}
+template <typename T> BCP_HD void store_manifold(T* f, size_t e, int m, const Manifold<T>& mf) {
+  if (mf.count <= 0) return;
+  T blk[BCP_MANI_STRIDE];
+  for (int k = 0; k < 4; ++k) {
+    T* q = blk + k * BCP_MANI_POINT;
+    const MPoint<T>& p = mf.p[k];
+    const bool live = k < mf.count;
+    for (int i = 0; i < 3; ++i) { q[i] = live ? p.la[i] : T(0); q[3 + i] = live ? p.lb[i] : T(0); q[6 + i] = live ? p.n[i] : T(0); }
+    q[9] = live ? p.dist : T(0);
+    q[10] = live ? p.imp : T(0);
+  }
+  store16(f + e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
+}
+template <typename T> BCP_HD void store_env_core(T* f, int* id, size_t e, const Env<T>& st) {
   T* r = f + e * NF;
   int* ir = id + e * NI;
   T head[BCP_S_MANI];
@@ -111,23 +123,23 @@ BCP_HD void store_env(T* __restrict__ f, int* __restrict__ id, size_t N, size_t 
   pack_body(st.pole, head + BCP_S_POLE);
   for (int i = 0; i < 3; ++i) { head[BCP_S_PEND_F + i] = st.pend_f[i]; head[BCP_S_PEND_T + i] = st.pend_t[i]; }
   store16(r, head, BCP_S_MANI);
-  for (int m = 0; m < 3; ++m) {
-    if (st.mani[m].count > 0) {
-      T blk[BCP_MANI_STRIDE];
-      for (int k = 0; k < 4; ++k) {
-        T* q = blk + k * BCP_MANI_POINT;
-        const MPoint<T>& p = st.mani[m].p[k];
-        const bool live = k < st.mani[m].count;
-        for (int i = 0; i < 3; ++i) { q[i] = live ? p.la[i] : T(0); q[3 + i] = live ? p.lb[i] : T(0); q[6 + i] = live ? p.n[i] : T(0); }
-        q[9] = live ? p.dist : T(0);
-        q[10] = live ? p.imp : T(0);
-      }
-      store16(r + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
-    }
-  }
   // the mode word (I_MODE) belongs to the split pipeline and is written by it
   ir[I_CNT] = st.mani[0].count; ir[I_CNT + 1] = st.mani[1].count; ir[I_CNT + 2] = st.mani[2].count;
   ir[I_STEPS] = st.steps; ir[I_DONE] = st.done; ir[I_EPISODE] = st.episode; ir[I_RESET_LEFT] = st.reset_left;
+}
+
+// the whole record.  `N` is unused (kept so that call sites read the same for any layout)
+template <typename T>
+BCP_HD void load_env(const T* __restrict__ f, const int* __restrict__ id, size_t N, size_t e, Env<T>& st) {
+  (void)N;
+  load_env_core(f, id, e, st);
+  for (int m = 0; m < 3; ++m) load_manifold(f, e, m, st.mani[m]);
+}
+template <typename T>
+BCP_HD void store_env(T* __restrict__ f, int* __restrict__ id, size_t N, size_t e, const Env<T>& st) {
+  (void)N;
+  store_env_core(f, id, e, st);
+  for (int m = 0; m < 3; ++m) store_manifold(f, e, m, st.mani[m]);
 }
 
 // canonical record (doubles, include/bcp.h) <-> register image
