@@ -252,23 +252,22 @@ def run_ours(args):
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- roofline of the dominant kernel: census of a state sample through the oracle ----
-    from oracle import Oracle
-    ns = min(n, 4096)
-    st = env.get_state()[:ns].copy()
-    busy = (st[:, C.S_DONE] == 0) | (st[:, C.S_RESET_LEFT] > 0)   # envs that run a substep next call
-    st[:, C.S_DONE] = 0
-    scfg = C.copy_config(env.cfg)
-    scfg.num_envs = ns
-    ora = Oracle(scfg, dtype="fp64")
-    ora.state[:] = st
-    info = ora.substep(with_info=True)
-    info[~busy] = 0
-    iters = float(info[busy, 0].mean()) if busy.any() else 0.0
-    rows_gc, rows_cp, rows_gp = (float(info[busy, 3 + k].mean()) for k in range(3))
-    flops_env = float(solve_flops(info, env.cfg).mean())
-    bytes_env = float(solve_bytes(info, env.cfg).mean())
+    # ---- census of the batch: what the solves of the last substep did (contact points per pair,
+    # PGS iterations), read back from the pipeline's own solve records on the GPU ----
     split = prof["n_solve"] > 0
+    if split:
+        li = env.last_solve_info().astype(np.int64)                       # (n, 4): gc, cp, gp points, iterations
+        busy = ((env.reward > 0) | (env.reason == C.REASON_RESETTING)).cpu().numpy()   # envs that ran that substep
+        info = np.zeros((n, 6), dtype=np.int64)
+        info[:, 0] = li[:, 3]
+        info[:, 3:6] = li[:, 0:3]
+        info[~busy] = 0
+        iters = float(info[busy, 0].mean()) if busy.any() else 0.0
+        rows_gc, rows_cp, rows_gp = (float(info[busy, 3 + k].mean()) for k in range(3))
+        flops_env = float(solve_flops(info, env.cfg).mean())
+        bytes_env = float(solve_bytes(info, env.cfg).mean())
+    else:  # the one-launch kernels keep no per-env solve record: no census, no flop view
+        info, busy, iters, rows_gc, rows_cp, rows_gp, flops_env, bytes_env = None, None, None, None, None, None, None, None
     lib = _lib.load()
     peak32, peak64 = ctypes.c_double(), ctypes.c_double()
     lib.bcp_bench_fma_peak(local, 0, 4096, ctypes.byref(peak32))
@@ -306,8 +305,7 @@ def run_ours(args):
     dom = kernels[dom_name]
     solve_name = "k_solve" if split else "k_step"
     solve_ms = kernels[solve_name]["launch_ms"]
-    flops_launch = flops_env * n * (1 if split else RS)
-    achieved_tf = flops_launch / (solve_ms * 1e-3) / 1e12
+    achieved_tf = flops_env * n / (solve_ms * 1e-3) / 1e12 if split else None
     value = live_all / (total_ms * 1e-3)
     out = {
         "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -341,13 +339,15 @@ def run_ours(args):
                      "note": "both kernels are issue-latency bound, not bandwidth bound (profiles/); "
                              "see roofline_kernels and roofline_pipe"},
         "roofline_kernels": kernels,
-        "roofline_pipe": {"bound": "fp32-cuda-core" if args.dtype == "fp32" else "fp64-cuda-core", "kernel": solve_name,
-                          "launch_ms": solve_ms, "share_of_step": kernels[solve_name]["share_of_step"],
-                          "achieved": achieved_tf, "peak": pipe_peak, "unit": "TFLOP/s", "frac": achieved_tf / pipe_peak,
-                          "peak_source": "bcp_bench_fma_peak (FMA chains, measured in this run)",
-                          "flops_per_env_solve": flops_env, "bytes_per_env_solve": bytes_env,
-                          "mean_solver_iterations": iters, "busy_fraction": float(busy.mean()),
-                          "mean_rows": {"ground_cart": rows_gc, "cart_pole": rows_cp, "ground_pole": rows_gp}},
+        "roofline_pipe": None if not split else {
+            "bound": "fp32-cuda-core", "kernel": solve_name,
+            "launch_ms": solve_ms, "share_of_step": kernels[solve_name]["share_of_step"],
+            "achieved": achieved_tf, "peak": pipe_peak, "unit": "TFLOP/s", "frac": achieved_tf / pipe_peak,
+            "peak_source": "bcp_bench_fma_peak (FMA chains, measured in this run)",
+            "flops_per_env_solve": flops_env, "bytes_per_env_solve": bytes_env,
+            "mean_solver_iterations": iters, "busy_fraction": float(busy.mean()),
+            "mean_rows": {"ground_cart": rows_gc, "cart_pole": rows_cp, "ground_pole": rows_gp},
+            "census": "bcp_last_solve_info: every env's solve record after the last timed call"},
     }
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(args)

@@ -11,7 +11,7 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libbcp.so")
 
 EXPORTS = ["bcp_abi_version", "bcp_config_size", "bcp_last_error", "bcp_create", "bcp_destroy", "bcp_reset",
            "bcp_step", "bcp_rollout_random", "bcp_stats", "bcp_stats_clear", "bcp_get_state", "bcp_set_state",
-           "bcp_substep", "bcp_launch_count", "bcp_bench_fma_peak", "bcp_profile_begin", "bcp_profile_end"]
+           "bcp_substep", "bcp_launch_count", "bcp_bench_fma_peak", "bcp_profile_begin", "bcp_profile_end", "bcp_last_solve_info"]
 
 
 class BcpError(RuntimeError):
@@ -48,6 +48,7 @@ def load(build_if_missing: bool = False):
     lib.bcp_launch_count.argtypes = [vp]
     lib.bcp_profile_begin.argtypes = [vp]
     lib.bcp_profile_end.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
+    lib.bcp_last_solve_info.argtypes = [vp, vp, ctypes.c_size_t, vp]
     lib.bcp_launch_count.restype = ctypes.c_int64
     if lib.bcp_abi_version() != C.BCP_ABI_VERSION:
         raise BcpError(f"libbcp.so ABI {lib.bcp_abi_version()} != python mirror {C.BCP_ABI_VERSION}: rebuild")

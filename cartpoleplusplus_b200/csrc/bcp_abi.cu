@@ -328,4 +328,18 @@ int bcp_profile_end(bcp_env* h, double* out4) {
   return 0;
 }
 
+int bcp_last_solve_info(bcp_env* h, int32_t* host_out, size_t n_ints, void* stream) {
+  if (!h || !host_out) return fail("bcp_last_solve_info: null argument");
+  if (h->f64() || !h->use_split || !h->split.recs) return fail("bcp_last_solve_info: the handle does not run the split pipeline");
+  if (n_ints != 4 * (size_t)h->cfg.num_envs) return fail("bcp_last_solve_info: n_ints must be 4 * num_envs");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  // the first four words of every record: three contact counts and the iteration count (bit patterns of ints)
+  const size_t pitch = bcp::split_record_words(h->p32) * sizeof(float);
+  CK(cudaMemcpy2DAsync(host_out, 4 * sizeof(int32_t), h->split.recs, pitch, 4 * sizeof(int32_t), (size_t)h->cfg.num_envs,
+                       cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
 }  // extern "C"

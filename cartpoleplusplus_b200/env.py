@@ -192,6 +192,13 @@ class BatchedBulletCartpole:
     def clear_stats(self):
         _lib.check(self._lib.bcp_stats_clear(self._h, self._stream()), self._lib)
 
+    def last_solve_info(self) -> np.ndarray:
+        """(B, 4) int32: contact points of the three pairs (ground-cart, cart-pole, ground-pole)
+        and PGS iterations of each env's last substep (split pipeline only; bench.py's census)."""
+        out = np.zeros((self.num_envs, 4), dtype=np.int32)
+        _lib.check(self._lib.bcp_last_solve_info(self._h, out.ctypes.data_as(ctypes.c_void_p), out.size, self._stream()), self._lib)
+        return out
+
     # ---- raw physics access used by parity tests ----
     def substep(self):
         _lib.check(self._lib.bcp_substep(self._h, self._stream()), self._lib)

@@ -235,6 +235,13 @@ int64_t bcp_launch_count(const bcp_env* env);
 int bcp_profile_begin(bcp_env* env);
 int bcp_profile_end(bcp_env* env, double* out4);
 
+/* Measurement helper (bench.py only): what the constraint solve of the LAST substep did, per
+ * env, read back from the split pipeline's solve records:
+ *   host_out[4 * e + 0..3] = { ground-cart, cart-pole, ground-pole contact points, PGS iterations }
+ * (stale for an env that did not run that substep).  n_ints = 4 * num_envs.  Synchronises.
+ * Error unless the handle runs the split pipeline (fp32, >= 4096 envs).                  */
+int bcp_last_solve_info(bcp_env* env, int32_t* host_out, size_t n_ints, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
