@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define BCP_ABI_VERSION 5
+#define BCP_ABI_VERSION 6
 
 /* ---- dtype of the physics arithmetic ------------------------------------ */
 #define BCP_DTYPE_F32 0 /* fast mode                                          */
