@@ -246,13 +246,13 @@ template <typename T> BCP_HD void finish_impulses(T* f, size_t e, int m, int cou
 template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
   return st.mani[0].count | (st.mani[1].count << 8) | (st.mani[2].count << 16);
 }
-#ifndef BCP_PREP_MINB
-#define BCP_PREP_MINB 4  // resident blocks per SM the register budget of k_prep is cut for
-#endif
 // s_fin: substep to finish (-1: none, this is the first kernel of the call)
 // s_set: substep to set up  (-1: none, this is the last kernel of the call)
-template <typename T, bool FRICTION>
-__global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
+// MINB: resident blocks per SM the register budget is cut for.  4 (128 registers, 16 warps per
+// SM) wins while the batch is about one wave (65 536 envs); 2 (199 registers, fewer spills, a
+// stack that fits L1 better) wins by 8-10 % once the batch is more than a wave (measured from 98 304 envs up).
+template <typename T, bool FRICTION, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
                                                  int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
                                                  int s_set) {
