@@ -9,8 +9,6 @@ size_t split_record_words(const Params<float>& P) { return (size_t)record_words(
 size_t split_counter_words(const Params<float>& P) { return (size_t)(P.R * P.S) * Q_WORDS; }
 size_t split_bins_words(const Params<float>& P) { return (size_t)N_BINS * (size_t)P.num_envs; }
 
-constexpr int kPrepWideRegsFrom = 90000;  // envs per GPU from which k_prep runs its 2-blocks-per-SM build (measured crossover between 65 536 and 98 304)
-
 template <bool FRICTION>
 static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, SplitBuffers& b, const SplitIO& io,
                                    const Stats& st, cudaStream_t s, int* launches, std::vector<cudaEvent_t>* prof) {
@@ -68,17 +66,10 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   }
   const int prep_grid = (N + prep_block - 1) / prep_block;
   mark();
-  static int wide = -1;  // BCP_PREP_WIDE=0/1 forces one build (tuning)
-  if (wide < 0) {
-    const char* w = getenv("BCP_PREP_WIDE");
-    wide = w ? (atoi(w) != 0 ? 1 : 0) : 2;
-  }
-  const bool many_waves = wide == 2 ? N >= kPrepWideRegsFrom : wide == 1;
   for (int k = 0; k <= RS; ++k) {
     const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
     int* qc = b.qc + (size_t)(k < RS ? k : 0) * Q_WORDS;
-    auto prep = many_waves ? k_prep<float, FRICTION, 2> : k_prep<float, FRICTION, 4>;
-    prep<<<prep_grid, prep_block, 0, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
+    k_prep<float, FRICTION><<<prep_grid, prep_block, 0, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
     if (launches) ++*launches;
     mark();
     if (k < RS) {

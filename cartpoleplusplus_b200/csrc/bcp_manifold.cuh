@@ -1,4 +1,7 @@
 // bcp_manifold.cuh — btPersistentManifold cache logic (included by bcp_collide.cuh).
+// Every access to the four cached points uses a compile-time index (unrolled loops with guards,
+// element selection by comparison instead of m.p[i] with a runtime i), so that a Manifold held
+// in a local variable stays in registers on the device instead of the thread's stack.
 #pragma once
 
 namespace bcp {
@@ -8,22 +11,27 @@ namespace bcp {
 template <typename T> BCP_HD int sort_cached_points(const Manifold<T>& m, const MPoint<T>& pt) {
   int maxPenetrationIndex = -1;
   T maxPenetration = pt.dist;
+#pragma unroll
   for (int i = 0; i < 4; ++i)
     if (m.p[i].dist < maxPenetration) { maxPenetrationIndex = i; maxPenetration = m.p[i].dist; }
   T res[4] = {0, 0, 0, 0};
   // (a0 index, b1 index, b2 index) per candidate: a = pt - p[ia]; b = p[ib1] - p[ib2]
-  const int ia[4] = {1, 0, 0, 0}, ib1[4] = {3, 3, 3, 2}, ib2[4] = {2, 2, 1, 1};
-  for (int c = 0; c < 4; ++c) {
-    if (maxPenetrationIndex != c) {
-      T a[3], b[3], cr[3];
-      for (int k = 0; k < 3; ++k) { a[k] = pt.la[k] - m.p[ia[c]].la[k]; b[k] = m.p[ib1[c]].la[k] - m.p[ib2[c]].la[k]; }
-      cross3(a, b, cr);
-      res[c] = dot3(cr, cr);
-    }
+#define BCP_AREA(c, ia, ib1, ib2)                                                                          \
+  if (maxPenetrationIndex != c) {                                                                          \
+    T a[3], b[3], cr[3];                                                                                   \
+    for (int k = 0; k < 3; ++k) { a[k] = pt.la[k] - m.p[ia].la[k]; b[k] = m.p[ib1].la[k] - m.p[ib2].la[k]; } \
+    cross3(a, b, cr);                                                                                      \
+    res[c] = dot3(cr, cr);                                                                                 \
   }
+  BCP_AREA(0, 1, 3, 2)
+  BCP_AREA(1, 0, 3, 2)
+  BCP_AREA(2, 0, 3, 1)
+  BCP_AREA(3, 0, 2, 1)
+#undef BCP_AREA
   // btVector4::closestAxis4 == maxAxis4 of absolute values
   int best = -1;
   T maxVal = -Lim<T>::large();
+#pragma unroll
   for (int i = 0; i < 4; ++i) {
     const T v = babs(res[i]);
     if (v > maxVal) { best = i; if (i < 3) maxVal = v; }
@@ -48,52 +56,67 @@ BCP_HD void manifold_add(Manifold<T>& m, const Posed<T>& A, const Posed<T>& B, c
   np.imp = 0;
   T shortest = breaking * breaking;
   int nearest = -1;
-  for (int i = 0; i < m.count; ++i) {
-    T d[3];
-    d[0] = m.p[i].la[0] - np.la[0]; d[1] = m.p[i].la[1] - np.la[1]; d[2] = m.p[i].la[2] - np.la[2];
-    const T dd = dot3(d, d);
-    if (dd < shortest) { shortest = dd; nearest = i; }
+  T near_imp = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if (i < m.count) {
+      T d[3];
+      d[0] = m.p[i].la[0] - np.la[0]; d[1] = m.p[i].la[1] - np.la[1]; d[2] = m.p[i].la[2] - np.la[2];
+      const T dd = dot3(d, d);
+      if (dd < shortest) { shortest = dd; nearest = i; near_imp = m.p[i].imp; }
+    }
   }
+  int insert;
   if (nearest >= 0) {
-    np.imp = m.p[nearest].imp;
-    m.p[nearest] = np;
+    np.imp = near_imp;
+    insert = nearest;
   } else {
-    int insert = m.count;
+    insert = m.count;
     if (insert == 4) insert = sort_cached_points(m, np);
     else m.count++;
     if (insert < 0) insert = 0;
-    m.p[insert] = np;
   }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (i == insert) m.p[i] = np;
 }
 
 // btPersistentManifold::refreshContactPoints; also yields the world points the
 // solver needs (positionWorldOnA/B).
 template <typename T>
 BCP_HD void manifold_refresh(Manifold<T>& m, const Posed<T>& A, const Posed<T>& B, T breaking, WorldPt<T> wp[4]) {
-  for (int i = m.count - 1; i >= 0; --i) {
-    MPoint<T>& p = m.p[i];
-    T d[3];
-    mat_mul_vec(A.R, p.la, wp[i].pa);
-    mat_mul_vec(B.R, p.lb, wp[i].pb);
-    for (int k = 0; k < 3; ++k) { wp[i].pa[k] += A.x[k]; wp[i].pb[k] += B.x[k]; }
-    for (int k = 0; k < 3; ++k) d[k] = wp[i].pa[k] - wp[i].pb[k];
-    p.dist = dot3(d, p.n);
-  }
-  for (int i = m.count - 1; i >= 0; --i) {
-    MPoint<T>& p = m.p[i];
-    bool remove = false;
-    if (!(p.dist <= breaking)) {
-      remove = true;
-    } else {
-      T proj[3], diff[3];
-      for (int k = 0; k < 3; ++k) proj[k] = wp[i].pa[k] - p.n[k] * p.dist;
-      for (int k = 0; k < 3; ++k) diff[k] = wp[i].pb[k] - proj[k];
-      if (dot3(diff, diff) > breaking * breaking) remove = true;
+#pragma unroll
+  for (int i = 3; i >= 0; --i) {
+    if (i < m.count) {
+      MPoint<T>& p = m.p[i];
+      T d[3];
+      mat_mul_vec(A.R, p.la, wp[i].pa);
+      mat_mul_vec(B.R, p.lb, wp[i].pb);
+      for (int k = 0; k < 3; ++k) { wp[i].pa[k] += A.x[k]; wp[i].pb[k] += B.x[k]; }
+      for (int k = 0; k < 3; ++k) d[k] = wp[i].pa[k] - wp[i].pb[k];
+      p.dist = dot3(d, p.n);
     }
-    if (remove) {
-      const int last = m.count - 1;
-      if (i != last) { m.p[i] = m.p[last]; wp[i] = wp[last]; }
-      m.count--;
+  }
+#pragma unroll
+  for (int i = 3; i >= 0; --i) {
+    if (i < m.count) {
+      MPoint<T>& p = m.p[i];
+      bool remove = false;
+      if (!(p.dist <= breaking)) {
+        remove = true;
+      } else {
+        T proj[3], diff[3];
+        for (int k = 0; k < 3; ++k) proj[k] = wp[i].pa[k] - p.n[k] * p.dist;
+        for (int k = 0; k < 3; ++k) diff[k] = wp[i].pb[k] - proj[k];
+        if (dot3(diff, diff) > breaking * breaking) remove = true;
+      }
+      if (remove) {  // the last point takes the removed one's slot
+        const int last = m.count - 1;
+#pragma unroll
+        for (int l = i + 1; l < 4; ++l)
+          if (l == last) { m.p[i] = m.p[l]; wp[i] = wp[l]; }
+        m.count--;
+      }
     }
   }
 }

@@ -346,7 +346,9 @@ BCP_HD void put_rows(const Params<T>& P, T* nrows, T* frows, T* apn, int m, int 
                      FBody<T>& A, FBody<T>& B) {
   const int W = TWO ? (int)SW2 : (int)SW1;
   const T rest = P.rest[m];
-  for (int j = 0; j < mf.count; ++j) {
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {  // compile-time indices into mf.p / wp (they stay in registers)
+    if (j >= mf.count) break;
     T* row = nrows + j * W;
     const T warm = (P.warmstart > T(0.0)) ? mf.p[j].imp * P.warmstart : T(0.0);
     if (TWO) apn[j] = put_row2(P, row, A, B, wp[j].pa, wp[j].pb, mf.p[j].n, mf.p[j].dist, rest, false, warm);

@@ -248,11 +248,12 @@ template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
 }
 // s_fin: substep to finish (-1: none, this is the first kernel of the call)
 // s_set: substep to set up  (-1: none, this is the last kernel of the call)
-// MINB: resident blocks per SM the register budget is cut for.  4 (128 registers, 16 warps per
-// SM) wins while the batch is about one wave (65 536 envs); 2 (199 registers, fewer spills, a
-// stack that fits L1 better) wins by 8-10 % once the batch is more than a wave (measured from 98 304 envs up).
-template <typename T, bool FRICTION, int MINB>
-__global__ void __launch_bounds__(kBlock, MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
+// Two resident blocks per SM: the register budget (up to 255) is what lets the manifold being
+// worked on, its world points and most of the row arithmetic stay in registers; at four blocks
+// per SM (128 registers) they spill to a stack that does not fit L1 (measured: 0.268 vs 0.245 ms
+// per env.step at 65 536 envs, 0.87 vs 0.70 ms at 262 144).
+template <typename T, bool FRICTION>
+__global__ void __launch_bounds__(kBlock, 2) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
                                                  int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
                                                  int s_set) {
@@ -309,7 +310,11 @@ __global__ void __launch_bounds__(kBlock, MINB) k_prep(const __grid_constant__ P
         Manifold<T> mf;
         mf.count = st.mani[m].count;
         load_manifold<T>(f, e, m, mf);
-        if (fin) for (int j = 0; j < mf.count; ++j) mf.p[j].imp = fin_apn[slot_of_pair(m) + j];
+        if (fin) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (j < mf.count) mf.p[j].imp = fin_apn[slot_of_pair(m) + j];
+        }
         setup_pair<T, FRICTION>(P, m, mf, C, rec, L);
         st.mani[m].count = mf.count;
         store_manifold<T>(f, e, m, mf);

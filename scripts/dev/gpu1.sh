@@ -6,4 +6,4 @@ python -c "
 import json; d=json.loads(open('gpurun_out/bench1.json').read().strip().splitlines()[-1]); print(d['value'], d['e2e']['value'], d['kernel_ms_per_step'])"
 export BCP_SPLIT=1
 python scripts/prof_split.py > gpurun_out/plain3.log 2>&1 && \
-ncu --set full --clock-control none --import-source on -k regex:k_solve -s 4 -c 1 -f -o gpurun_out/prof_r1_solve5 python scripts/prof_split.py > gpurun_out/ncu3.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_prep -s 7 -c 1 -f -o gpurun_out/prof_r1_prep4 python scripts/prof_split.py > gpurun_out/ncu3.log 2>&1

@@ -53,11 +53,8 @@ def test_bookkeeping_identities_at_full_size(built):
 
 @pytest.mark.parametrize("N", [65536, 131072])
 def test_trajectories_do_not_depend_on_the_sharding(built, N):
-    """Whole batch vs two half-size handles with env_id_offset: bit for bit when both sides run
-    the same build of k_prep (65 536 vs 2 x 32 768).  At 131 072 the whole batch runs k_prep's
-    2-blocks-per-SM build and the halves the 4-blocks-per-SM one; ptxas contracts FMAs
-    differently in the two, so there the trajectories agree to fp32 rounding instead."""
-    exact = N < 90000
+    """Whole batch vs two half-size handles with env_id_offset: bit for bit, at both sizes."""
+    exact = True
     whole = _env(N, initial_force=55.0)
     halves = [_env(N // 2, offset=0, initial_force=55.0), _env(N // 2, offset=N // 2, initial_force=55.0)]
     def same(x, y):
