@@ -69,19 +69,31 @@ template <typename T> BCP_HD void setup_begin(const Params<T>& P, const Env<T>& 
 }
 template <typename T, bool FRICTION>
 BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, SetupCtx<T>& C, T* rec, const SolveLayout& L) {
-  const Posed<T>& A = (m == BCP_PAIR_CART_POLE) ? C.cbox : C.gbox;
-  const Posed<T>& B = (m == BCP_PAIR_GROUND_CART) ? C.cbox : C.pbox;
+  const Posed<T>& Am = (m == BCP_PAIR_CART_POLE) ? C.cbox : C.gbox;
+  const Posed<T>& Bm = (m == BCP_PAIR_GROUND_CART) ? C.cbox : C.pbox;
   Contact<T> cs[4];
   WorldPt<T> wp[4];
-  const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, cs);
+  const int nc = box_box(Am.x, Am.R, Am.h, Bm.x, Bm.R, Bm.h, cs);
+  const Posed<T> A = Am, B = Bm;  // by value: read once, then registers (the narrowphase needs them in memory)
   for (int k = 0; k < nc; ++k) manifold_add(mf, A, B, cs[k], P.breaking[m]);
   manifold_refresh(mf, A, B, P.breaking[m], wp);
   T* rows = rec + REC_ROWS + L.base[m];
   T* frows = rec + REC_ROWS + (L.fbase[m] >= 0 ? L.fbase[m] : 0);
   T* apn = C.apn_all + slot_of_pair(m);
-  if (m == BCP_PAIR_GROUND_CART) put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, C.cart, C.cart);
-  else if (m == BCP_PAIR_CART_POLE) put_rows<T, FRICTION, true>(P, rows, frows, apn, m, L.rpc[m], mf, wp, C.cart, C.pole);
-  else put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, C.pole, C.pole);
+  // the bodies by value while the rows are built (registers); only the warm-start deltas go back
+  if (m == BCP_PAIR_GROUND_CART) {
+    FBody<T> cart = C.cart;
+    put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, cart, cart);
+    for (int i = 0; i < 3; ++i) { C.cart.dwl[i] = cart.dwl[i]; C.cart.dv[i] = cart.dv[i]; }
+  } else if (m == BCP_PAIR_CART_POLE) {
+    FBody<T> cart = C.cart, pole = C.pole;
+    put_rows<T, FRICTION, true>(P, rows, frows, apn, m, L.rpc[m], mf, wp, cart, pole);
+    for (int i = 0; i < 3; ++i) { C.cart.dwl[i] = cart.dwl[i]; C.cart.dv[i] = cart.dv[i]; C.pole.dwl[i] = pole.dwl[i]; C.pole.dv[i] = pole.dv[i]; }
+  } else {
+    FBody<T> pole = C.pole;
+    put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, pole, pole);
+    for (int i = 0; i < 3; ++i) { C.pole.dwl[i] = pole.dwl[i]; C.pole.dv[i] = pole.dv[i]; }
+  }
 }
 template <typename T> BCP_HD void setup_end(const Params<T>& P, Env<T>& st, const SetupCtx<T>& C, T* rec) {
   rec[REC_C_GC] = as_real(st.mani[BCP_PAIR_GROUND_CART].count, T(0));
@@ -252,8 +264,11 @@ template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
 // worked on, its world points and most of the row arithmetic stay in registers; at four blocks
 // per SM (128 registers) they spill to a stack that does not fit L1 (measured: 0.268 vs 0.245 ms
 // per env.step at 65 536 envs, 0.87 vs 0.70 ms at 262 144).
+#ifndef BCP_PREP_MINB
+#define BCP_PREP_MINB 2
+#endif
 template <typename T, bool FRICTION>
-__global__ void __launch_bounds__(kBlock, 2) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
+__global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
                                                  int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
                                                  int s_set) {
