@@ -52,6 +52,7 @@ BCP_HD int slot_of_pair(int m) { return m == BCP_PAIR_GROUND_CART ? (int)SLOT_GC
 // The setup in pieces, so that k_prep can stream the manifolds through it one pair at a time:
 // setup_begin (poses, forward dynamics), setup_pair x 3 (narrowphase, manifold cache, rows),
 // setup_end (record header, velocities parked in the state).
+template <typename V> BCP_HD V pick3(const V* a, int m) { return m == 0 ? a[0] : (m == 1 ? a[1] : a[2]); }
 template <typename T> struct SetupCtx {
   Posed<T> gbox, cbox, pbox;
   FBody<T> cart, pole;
@@ -75,23 +76,27 @@ BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, SetupCtx<T>& 
   WorldPt<T> wp[4];
   const int nc = box_box(Am.x, Am.R, Am.h, Bm.x, Bm.R, Bm.h, cs);
   const Posed<T> A = Am, B = Bm;  // by value: read once, then registers (the narrowphase needs them in memory)
-  for (int k = 0; k < nc; ++k) manifold_add(mf, A, B, cs[k], P.breaking[m]);
-  manifold_refresh(mf, A, B, P.breaking[m], wp);
-  T* rows = rec + REC_ROWS + L.base[m];
-  T* frows = rec + REC_ROWS + (L.fbase[m] >= 0 ? L.fbase[m] : 0);
+  // per-pair constants picked by comparison: an array in constant memory indexed by a register
+  // is a slow, scoreboarded load
+  const T brk = pick3(P.breaking, m);
+  const int base = pick3(L.base, m), fbase = pick3(L.fbase, m), rpc = pick3(L.rpc, m);
+  for (int k = 0; k < nc; ++k) manifold_add(mf, A, B, cs[k], brk);
+  manifold_refresh(mf, A, B, brk, wp);
+  T* rows = rec + REC_ROWS + base;
+  T* frows = rec + REC_ROWS + (fbase >= 0 ? fbase : 0);
   T* apn = C.apn_all + slot_of_pair(m);
   // the bodies by value while the rows are built (registers); only the warm-start deltas go back
   if (m == BCP_PAIR_GROUND_CART) {
     FBody<T> cart = C.cart;
-    put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, cart, cart);
+    put_rows<T, FRICTION, false>(P, rows, frows, apn, BCP_PAIR_GROUND_CART, rpc, mf, wp, cart, cart);
     for (int i = 0; i < 3; ++i) { C.cart.dwl[i] = cart.dwl[i]; C.cart.dv[i] = cart.dv[i]; }
   } else if (m == BCP_PAIR_CART_POLE) {
     FBody<T> cart = C.cart, pole = C.pole;
-    put_rows<T, FRICTION, true>(P, rows, frows, apn, m, L.rpc[m], mf, wp, cart, pole);
+    put_rows<T, FRICTION, true>(P, rows, frows, apn, BCP_PAIR_CART_POLE, rpc, mf, wp, cart, pole);
     for (int i = 0; i < 3; ++i) { C.cart.dwl[i] = cart.dwl[i]; C.cart.dv[i] = cart.dv[i]; C.pole.dwl[i] = pole.dwl[i]; C.pole.dv[i] = pole.dv[i]; }
   } else {
     FBody<T> pole = C.pole;
-    put_rows<T, FRICTION, false>(P, rows, frows, apn, m, L.rpc[m], mf, wp, pole, pole);
+    put_rows<T, FRICTION, false>(P, rows, frows, apn, BCP_PAIR_GROUND_POLE, rpc, mf, wp, pole, pole);
     for (int i = 0; i < 3; ++i) { C.pole.dwl[i] = pole.dwl[i]; C.pole.dv[i] = pole.dv[i]; }
   }
 }
