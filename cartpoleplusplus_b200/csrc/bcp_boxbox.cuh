@@ -5,9 +5,17 @@
 
 namespace bcp {
 
+// Workspace of one call, supplied by the caller (k_prep: the thread's shared-memory frame, so
+// that the clipper's register-indexed arrays never touch the thread's stack; elsewhere a local
+// array).  The <= 4 contacts come back in its first words, over the clipper's arrays, which are
+// dead by then.
+constexpr int kBoxWs = 72;
+template <typename T> BCP_HD const Contact<T>* box_contacts(const T* ws) { return reinterpret_cast<const Contact<T>*>(ws); }
+
 template <typename T>
-BCP_HD_NOINLINE int box_box(const T p1[3], const T* R1, const T h1[3], const T p2[3], const T* R2, const T h2[3],
-                            Contact<T> out[4]) {
+BCP_HD_NOINLINE int box_box(const T p1[3], const T* R1, const T h1[3], const T p2[3], const T* R2, const T h2[3], T* ws) {
+  Contact<T>* const out = reinterpret_cast<Contact<T>*>(ws);                                   // [0, 28)
+  T *const quad = ws, *const ret = ws + 8, *const buffer = ws + 24, *const point = ws + 40, *const dep = ws + 64;
   const T fudge_factor = T(1.05);
   const T fudge2 = (T)1.0e-5f;
   T p[3], pp[3], normalC[3] = {0, 0, 0}, normal[3];
@@ -117,7 +125,7 @@ BCP_HD_NOINLINE int box_box(const T p1[3], const T* R1, const T h1[3], const T p
 
   // face-something: reference face on box a, incident face on box b
   const T *Ra, *Rb, *pa, *pb, *Sa, *Sb;
-  T normal2[3], nr[3], anr[3], center[3], quad[8], rect[2], ret[16], point[3 * 8], dep[8];
+  T normal2[3], nr[3], anr[3], center[3], rect[2];
   int lanr, a1, a2, codeN, code1, code2, maxc = 4;
   if (code <= 3) { Ra = R1; Rb = R2; pa = p1; pb = p2; Sa = A; Sb = B; }
   else { Ra = R2; Rb = R1; pa = p2; pb = p1; Sa = B; Sb = A; }
@@ -156,7 +164,7 @@ BCP_HD_NOINLINE int box_box(const T p1[3], const T* R1, const T h1[3], const T p
   }
   rect[0] = Sa[code1];
   rect[1] = Sa[code2];
-  const int n = intersect_rect_quad(rect, quad, ret);
+  const int n = intersect_rect_quad(rect, quad, ret, buffer);
   if (n < 1) return 0;
   const T det1 = T(1.0) / (m11 * m22 - m12 * m21);
   m11 *= det1; m12 *= det1; m21 *= det1; m22 *= det1;
@@ -186,20 +194,21 @@ BCP_HD_NOINLINE int box_box(const T p1[3], const T* R1, const T h1[3], const T p
     }
     return cnum;
   }
-  int i1 = 0, iret[8];
+  int i1 = 0;
   T maxdepth = dep[0];
   for (int i = 1; i < cnum; ++i)
     if (dep[i] > maxdepth) { maxdepth = dep[i]; i1 = i; }
-  cull_points(cnum, ret, maxc, i1, iret);
+  const unsigned picks = cull_points(cnum, ret, maxc, i1, buffer);
   for (int j = 0; j < maxc; ++j) {
+    const int ij = (int)((picks >> (4 * j)) & 15u);
     T pw[3];
-    for (int i = 0; i < 3; ++i) pw[i] = point[iret[j] * 3 + i] + pa[i];
+    for (int i = 0; i < 3; ++i) pw[i] = point[ij * 3 + i] + pa[i];
     for (int i = 0; i < 3; ++i) {
       out[j].n[i] = -normal[i];
       if (code < 4) out[j].pb[i] = pw[i];
-      else out[j].pb[i] = pw[i] - normal[i] * dep[iret[j]];
+      else out[j].pb[i] = pw[i] - normal[i] * dep[ij];
     }
-    out[j].depth = -dep[iret[j]];
+    out[j].depth = -dep[ij];
   }
   return maxc;
 }

@@ -38,9 +38,9 @@ template <typename T> BCP_HD T dot_vc(const T* v, const T* A, int ja) {
 }
 
 // intersectRectQuad2: clip the quad p[8] against the rectangle +-h; <= 8 points.
-template <typename T> BCP_HD_NOINLINE int intersect_rect_quad(const T h[2], T p[8], T ret[16]) {
+// `buffer` is the second ping-pong array (caller's workspace, see box_box).
+template <typename T> BCP_HD_NOINLINE int intersect_rect_quad(const T h[2], T p[8], T ret[16], T buffer[16]) {
   int nq = 4, nr = 0;
-  T buffer[16];
   T* q = p;
   T* r = ret;
   for (int dir = 0; dir <= 1; ++dir) {
@@ -77,11 +77,11 @@ done:
   return nr;
 }
 
-// cullPoints2: choose m of the n clipped points, spread in angle, i0 first.
-template <typename T> BCP_HD_NOINLINE void cull_points(int n, const T p[], int m, int i0, int iret[]) {
+// cullPoints2: choose m (<= 8) of the n clipped points, spread in angle, i0 first.
+// Returns the chosen indices packed four bits each (j-th pick in bits 4j..4j+3); `A` is an
+// 8-word scratch array from the caller's workspace, the "still available" flags are a bit mask.
+template <typename T> BCP_HD_NOINLINE unsigned cull_points(int n, const T p[], int m, int i0, T A[8]) {
   T a, cx, cy, q;
-  T A[8];
-  int avail[8];
   const float M__PI = 3.14159265f;  // Bullet's float literal
   if (n == 1) {
     cx = p[0];
@@ -104,28 +104,28 @@ template <typename T> BCP_HD_NOINLINE void cull_points(int n, const T p[], int m
     cy = a * (cy + q * (p[n * 2 - 1] + p[1]));
   }
   for (int i = 0; i < n; ++i) A[i] = det_atan2(p[i * 2 + 1] - cy, p[i * 2] - cx);
-  for (int i = 0; i < n; ++i) avail[i] = 1;
-  avail[i0] = 0;
-  iret[0] = i0;
-  iret++;
+  unsigned avail = ((1u << n) - 1u) & ~(1u << i0);
+  unsigned picks = (unsigned)i0;
+  const T A0 = A[i0];
   for (int j = 1; j < m; ++j) {
     T maxdiff = T(1e9), diff;
-    a = (T)j * (T)(2 * M__PI / (float)m) + A[i0];
+    a = (T)j * (T)(2 * M__PI / (float)m) + A0;
     if (a > (T)M__PI) a -= (T)(2 * M__PI);
-    *iret = i0;
+    int pick = i0;
     for (int i = 0; i < n; ++i) {
-      if (avail[i]) {
+      if ((avail >> i) & 1u) {
         diff = babs(A[i] - a);
         if (diff > (T)M__PI) diff = (T)(2 * M__PI) - diff;
         if (diff < maxdiff) {
           maxdiff = diff;
-          *iret = i;
+          pick = i;
         }
       }
     }
-    avail[*iret] = 0;
-    iret++;
+    avail &= ~(1u << pick);
+    picks |= (unsigned)pick << (4 * j);
   }
+  return picks;
 }
 
 template <typename T>

@@ -38,8 +38,9 @@ BCP_HD_NOINLINE void substep(const Params<T>& P, Env<T>& st, SubstepInfo* info) 
   for (int m = 0; m < 3; ++m) {
     const Posed<T>& A = box[pairA[m]];
     const Posed<T>& B = box[pairB[m]];
-    Contact<T> cs[4];
-    const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, cs);
+    T ws[kBoxWs];
+    const Contact<T>* cs = box_contacts(ws);
+    const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, ws);
     for (int k = 0; k < nc; ++k) manifold_add(st.mani[m], A, B, cs[k], P.breaking[m]);
     manifold_refresh(st.mani[m], A, B, P.breaking[m], wp[m]);
     if (info) info->contacts[m] = st.mani[m].count;

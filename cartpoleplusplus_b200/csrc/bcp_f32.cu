@@ -65,11 +65,14 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
     if (prep_block < 32 || prep_block > kBlock || prep_block % 32) prep_block = kBlock;
   }
   const int prep_grid = (N + prep_block - 1) / prep_block;
+  const size_t prep_smem = prep_smem_bytes(prep_block);
+  err = allow_smem(k_prep<float, FRICTION>, prep_smem);
+  if (err != cudaSuccess) return err;
   mark();
   for (int k = 0; k <= RS; ++k) {
     const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
     int* qc = b.qc + (size_t)(k < RS ? k : 0) * Q_WORDS;
-    k_prep<float, FRICTION><<<prep_grid, prep_block, 0, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
+    k_prep<float, FRICTION><<<prep_grid, prep_block, prep_smem, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
     if (launches) ++*launches;
     mark();
     if (k < RS) {

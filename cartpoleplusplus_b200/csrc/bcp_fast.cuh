@@ -343,9 +343,10 @@ BCP_HD void fast_setup(const Params<T>& P, Env<T>& st, const Col<T>& col, const 
     if (on) {
       const Posed<T>& A = (m == BCP_PAIR_CART_POLE) ? cbox : gbox;
       const Posed<T>& B = (m == BCP_PAIR_GROUND_CART) ? cbox : pbox;
-      Contact<T> cs[4];
+      T ws[kBoxWs];
+      const Contact<T>* cs = box_contacts(ws);
       WorldPt<T> wp[4];
-      const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, cs);
+      const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, ws);
       for (int k = 0; k < nc; ++k) manifold_add(st.mani[m], A, B, cs[k], P.breaking[m]);
       manifold_refresh(st.mani[m], A, B, P.breaking[m], wp);
       if (m == BCP_PAIR_GROUND_CART) build_rows<T, FRICTION, false>(P, col, m, L.base[m], L.w[m], st.mani[m], wp, cart, cart);

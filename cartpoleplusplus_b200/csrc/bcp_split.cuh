@@ -53,29 +53,42 @@ BCP_HD int slot_of_pair(int m) { return m == BCP_PAIR_GROUND_CART ? (int)SLOT_GC
 // setup_begin (poses, forward dynamics), setup_pair x 3 (narrowphase, manifold cache, rows),
 // setup_end (record header, velocities parked in the state).
 template <typename V> BCP_HD V pick3(const V* a, int m) { return m == 0 ? a[0] : (m == 1 ? a[1] : a[2]); }
+// The context is in three parts on purpose: the posed boxes and the narrowphase workspace are
+// handed to box_box by address (k_prep keeps them in the thread's shared-memory frame), while
+// the bodies and the impulse slots are only ever touched with compile-time offsets, so they
+// stay in registers.
+template <typename T> struct SetupFrame {  // what box_box reads and scribbles on
+  Posed<T> cbox, pbox;
+  T ws[kBoxWs];
+};
 template <typename T> struct SetupCtx {
-  Posed<T> gbox, cbox, pbox;
   FBody<T> cart, pole;
   T apn_all[N_SLOTS];
 };
-template <typename T> BCP_HD void setup_begin(const Params<T>& P, const Env<T>& st, SetupCtx<T>& C) {
-  for (int i = 0; i < 3; ++i) { C.gbox.x[i] = P.ground.x0[i]; C.gbox.h[i] = P.ground.h[i]; }
-  for (int i = 0; i < 9; ++i) C.gbox.R[i] = (i % 4 == 0) ? T(1.0) : T(0.0);
-  pose_box(st.cart, P.cart, C.cbox);
-  pose_box(st.pole, P.pole, C.pbox);
+template <typename T> BCP_HD void ground_box(const Params<T>& P, Posed<T>& g) {
+  for (int i = 0; i < 3; ++i) { g.x[i] = P.ground.x0[i]; g.h[i] = P.ground.h[i]; }
+  for (int i = 0; i < 9; ++i) g.R[i] = (i % 4 == 0) ? T(1.0) : T(0.0);
+}
+template <typename T> BCP_HD void setup_begin(const Params<T>& P, const Env<T>& st, SetupFrame<T>& F, SetupCtx<T>& C) {
+  Posed<T> cb, pb;  // registers first: the frame only ever sees stores
+  pose_box(st.cart, P.cart, cb);
+  pose_box(st.pole, P.pole, pb);
   const T zero3[3] = {0, 0, 0};
-  fbody_begin(P, st.cart, P.cart, C.cbox.R, st.pend_f, st.pend_t, C.cart);
-  fbody_begin(P, st.pole, P.pole, C.pbox.R, zero3, zero3, C.pole);
+  fbody_begin(P, st.cart, P.cart, cb.R, st.pend_f, st.pend_t, C.cart);
+  fbody_begin(P, st.pole, P.pole, pb.R, zero3, zero3, C.pole);
+  F.cbox = cb;
+  F.pbox = pb;
   for (int k = 0; k < N_SLOTS; ++k) C.apn_all[k] = T(0.0);
 }
 template <typename T, bool FRICTION>
-BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, SetupCtx<T>& C, T* rec, const SolveLayout& L) {
-  const Posed<T>& Am = (m == BCP_PAIR_CART_POLE) ? C.cbox : C.gbox;
-  const Posed<T>& Bm = (m == BCP_PAIR_GROUND_CART) ? C.cbox : C.pbox;
-  Contact<T> cs[4];
+BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, const Posed<T>& gbox, SetupFrame<T>& F, SetupCtx<T>& C,
+                       T* rec, const SolveLayout& L) {
+  const Posed<T>& Am = (m == BCP_PAIR_CART_POLE) ? F.cbox : gbox;
+  const Posed<T>& Bm = (m == BCP_PAIR_GROUND_CART) ? F.cbox : F.pbox;
   WorldPt<T> wp[4];
-  const int nc = box_box(Am.x, Am.R, Am.h, Bm.x, Bm.R, Bm.h, cs);
-  const Posed<T> A = Am, B = Bm;  // by value: read once, then registers (the narrowphase needs them in memory)
+  const int nc = box_box(Am.x, Am.R, Am.h, Bm.x, Bm.R, Bm.h, F.ws);
+  const Contact<T>* cs = box_contacts(F.ws);
+  const Posed<T> A = Am, B = Bm;  // by value: read once, then registers
   // per-pair constants picked by comparison: an array in constant memory indexed by a register
   // is a slow, scoreboarded load
   const T brk = pick3(P.breaking, m);
@@ -84,20 +97,12 @@ BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, SetupCtx<T>& 
   manifold_refresh(mf, A, B, brk, wp);
   T* rows = rec + REC_ROWS + base;
   T* frows = rec + REC_ROWS + (fbase >= 0 ? fbase : 0);
-  T* apn = C.apn_all + slot_of_pair(m);
-  // the bodies by value while the rows are built (registers); only the warm-start deltas go back
   if (m == BCP_PAIR_GROUND_CART) {
-    FBody<T> cart = C.cart;
-    put_rows<T, FRICTION, false>(P, rows, frows, apn, BCP_PAIR_GROUND_CART, rpc, mf, wp, cart, cart);
-    for (int i = 0; i < 3; ++i) { C.cart.dwl[i] = cart.dwl[i]; C.cart.dv[i] = cart.dv[i]; }
+    put_rows<T, FRICTION, false>(P, rows, frows, C.apn_all + slot_of_pair(BCP_PAIR_GROUND_CART), BCP_PAIR_GROUND_CART, rpc, mf, wp, C.cart, C.cart);
   } else if (m == BCP_PAIR_CART_POLE) {
-    FBody<T> cart = C.cart, pole = C.pole;
-    put_rows<T, FRICTION, true>(P, rows, frows, apn, BCP_PAIR_CART_POLE, rpc, mf, wp, cart, pole);
-    for (int i = 0; i < 3; ++i) { C.cart.dwl[i] = cart.dwl[i]; C.cart.dv[i] = cart.dv[i]; C.pole.dwl[i] = pole.dwl[i]; C.pole.dv[i] = pole.dv[i]; }
+    put_rows<T, FRICTION, true>(P, rows, frows, C.apn_all + slot_of_pair(BCP_PAIR_CART_POLE), BCP_PAIR_CART_POLE, rpc, mf, wp, C.cart, C.pole);
   } else {
-    FBody<T> pole = C.pole;
-    put_rows<T, FRICTION, false>(P, rows, frows, apn, BCP_PAIR_GROUND_POLE, rpc, mf, wp, pole, pole);
-    for (int i = 0; i < 3; ++i) { C.pole.dwl[i] = pole.dwl[i]; C.pole.dv[i] = pole.dv[i]; }
+    put_rows<T, FRICTION, false>(P, rows, frows, C.apn_all + slot_of_pair(BCP_PAIR_GROUND_POLE), BCP_PAIR_GROUND_POLE, rpc, mf, wp, C.pole, C.pole);
   }
 }
 template <typename T> BCP_HD void setup_end(const Params<T>& P, Env<T>& st, const SetupCtx<T>& C, T* rec) {
@@ -119,9 +124,12 @@ template <typename T, bool FRICTION>
 BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
   if (!on) return;
   SetupCtx<T> C;
+  SetupFrame<T> F;
+  Posed<T> gbox;
+  ground_box(P, gbox);
   const SolveLayout L = solve_layout(P);
-  setup_begin(P, st, C);
-  for (int m = 0; m < 3; ++m) setup_pair<T, FRICTION>(P, m, st.mani[m], C, rec, L);
+  setup_begin(P, st, F, C);
+  for (int m = 0; m < 3; ++m) setup_pair<T, FRICTION>(P, m, st.mani[m], gbox, F, C, rec, L);
   setup_end(P, st, C, rec);
 }
 
@@ -272,6 +280,10 @@ template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
 #ifndef BCP_PREP_MINB
 #define BCP_PREP_MINB 2
 #endif
+// k_prep's dynamic shared memory: the ground box, then one SetupFrame per thread
+constexpr int kPrepGround = 16;
+constexpr int kPrepFrame = (int)(sizeof(SetupFrame<float>) / sizeof(float)) | 1;
+inline size_t prep_smem_bytes(int block) { return sizeof(float) * ((size_t)kPrepGround + (size_t)block * kPrepFrame); }
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
@@ -321,8 +333,14 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     const int last_iters = on ? as_int(rec[REC_ITERS]) : 0;
     SetupCtx<T> C;
     const SolveLayout L = solve_layout(P);
-    BCP_WARP_SYNC();
-    if (on) setup_begin(P, st, C);
+    // the thread's frame in shared memory ([thread][kPrepFrame] words, odd stride: conflict-free
+    // when the lanes of a warp touch the same member); the ground box once per block
+    T* const smem = reinterpret_cast<T*>(bcp_smem);
+    Posed<T>& gbox = *reinterpret_cast<Posed<T>*>(smem);
+    SetupFrame<T>& F = *reinterpret_cast<SetupFrame<T>*>(smem + kPrepGround + (size_t)threadIdx.x * kPrepFrame);
+    if (threadIdx.x == 0) ground_box(P, gbox);
+    __syncthreads();
+    if (on) setup_begin(P, st, F, C);
 #pragma unroll 1
     for (int m = 0; m < 3; ++m) {
       BCP_WARP_SYNC();
@@ -335,7 +353,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
           for (int j = 0; j < 4; ++j)
             if (j < mf.count) mf.p[j].imp = fin_apn[slot_of_pair(m) + j];
         }
-        setup_pair<T, FRICTION>(P, m, mf, C, rec, L);
+        setup_pair<T, FRICTION>(P, m, mf, gbox, F, C, rec, L);
         st.mani[m].count = mf.count;
         store_manifold<T>(f, e, m, mf);
       } else if (fin) {
