@@ -177,11 +177,11 @@ template <typename T> BCP_HD void solve_end(T* rec, const SolveScale<T>& S, int 
 
 // finish half of a substep: velocities += deltas, integrate (finish_bodies), impulses ->
 // manifold cache (split_finish adds that for a fully loaded env; k_prep does it per pair)
-template <typename T> BCP_HD void finish_bodies(const Params<T>& P, Env<T>& st, const T* rec) {
+template <typename T> BCP_HD void finish_bodies(const Params<T>& P, Env<T>& st, const T* dvel) {  // dvel: the record's REC_DVEL block
   FBody<T> cart, pole;
   for (int i = 0; i < 3; ++i) {
-    cart.dwl[i] = rec[REC_DVEL + i]; cart.dv[i] = rec[REC_DVEL + 3 + i];
-    pole.dwl[i] = rec[REC_DVEL + 6 + i]; pole.dv[i] = rec[REC_DVEL + 9 + i];
+    cart.dwl[i] = dvel[i]; cart.dv[i] = dvel[3 + i];
+    pole.dwl[i] = dvel[6 + i]; pole.dv[i] = dvel[9 + i];
     cart.wl[i] = st.cart.w[i]; cart.v[i] = st.cart.v[i];
     pole.wl[i] = st.pole.w[i]; pole.v[i] = st.pole.v[i];
   }
@@ -193,7 +193,7 @@ template <typename T> BCP_HD void finish_bodies(const Params<T>& P, Env<T>& st, 
 template <typename T> BCP_HD void split_finish(const Params<T>& P, Env<T>& st, const T* rec) {
   for (int m = 0; m < 3; ++m)
     for (int j = 0; j < st.mani[m].count; ++j) st.mani[m].p[j].imp = rec[REC_APN + slot_of_pair(m) + j];
-  finish_bodies(P, st, rec);
+  finish_bodies(P, st, rec + REC_DVEL);
 }
 
 // host-side composition (tests): the whole substep through a record, one env.  Slots the env
@@ -284,6 +284,7 @@ template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
 constexpr int kPrepGround = 16;
 constexpr int kPrepFrame = (int)(sizeof(SetupFrame<float>) / sizeof(float)) | 1;
 inline size_t prep_smem_bytes(int block) { return sizeof(float) * ((size_t)kPrepGround + (size_t)block * kPrepFrame); }
+__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
@@ -302,26 +303,45 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   st.reset_left = 0;
   int mode = MODE_IDLE;
   for (int m = 0; m < 3; ++m) st.mani[m].count = 0;
+  // Everything this env will need from global memory whose address only depends on the env id
+  // is requested here, before any of it is used and whether or not its phase will use it: the
+  // state core, the previous solve's results in the record, the action.  One exposed DRAM
+  // latency instead of one per dependent decision (a thread has nothing else to overlap it with
+  // at two warps per scheduler).
+  T fin_apn[N_SLOTS];  // applied normal impulses of the solve being finished -> manifold caches
+  T fin_dvel[12];      // its velocity deltas
+  int act_i = 0, last_iters = 0;
+  float2 act_f = make_float2(0.f, 0.f);
   if (valid) {
+    if (s_fin >= 0) {
+      for (int k = 0; k < 3; ++k) { ld4(rec + REC_APN + 4 * k, fin_apn + 4 * k); ld4(rec + REC_DVEL + 4 * k, fin_dvel + 4 * k); }
+      if (io.actions) {
+        if (P.discrete) act_i = reinterpret_cast<const int32_t*>(io.actions)[e];
+        else act_f = reinterpret_cast<const float2*>(io.actions)[e];
+      }
+    }
+    if (s_set >= 0) last_iters = as_int(rec[REC_ITERS]);
     load_env_core<T>(f, id, e, st);  // the manifold points are streamed per pair below
     mode = id[(size_t)e * NI + I_MODE];
+    if (s_set >= 0) {  // ... and their blocks are asked into L2 now
+#pragma unroll
+      for (int m = 0; m < 3; ++m)
+        if (st.mani[m].count > 0) {
+          const T* blk = f + (size_t)e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE;
+          prefetch_l2(blk);
+          prefetch_l2(blk + BCP_MANI_STRIDE - 1);
+        }
+    }
   }
   if (s_fin < 0) mode = call_begin(P, st, valid);
   const bool fin = s_fin >= 0 && valid && substep_on(mode, st);
-  T fin_apn[N_SLOTS];  // applied normal impulses of the solve being finished -> manifold caches
-  if (fin) {
-    for (int k = 0; k < 3; ++k) ld4(rec + REC_APN + 4 * k, fin_apn + 4 * k);
-    finish_bodies(P, st, rec);
-  }
+  if (fin) finish_bodies(P, st, fin_dvel);
   if (s_fin >= 0 && valid) {
     int a = 0;
     float ax = 0.f, ay = 0.f;
     if (mode == MODE_LIVE) {
-      if (P.discrete) a = reinterpret_cast<const int32_t*>(io.actions)[e];
-      else {
-        const float2 av = reinterpret_cast<const float2*>(io.actions)[e];
-        ax = av.x; ay = av.y;
-      }
+      a = act_i;
+      ax = act_f.x; ay = act_f.y;
     }
     T fx, fy;
     action_force(P, a, ax, ay, fx, fy);
@@ -330,7 +350,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   }
   if (s_set >= 0) {
     const bool on = valid && substep_on(mode, st);
-    const int last_iters = on ? as_int(rec[REC_ITERS]) : 0;
+    if (!on) last_iters = 0;
     SetupCtx<T> C;
     const SolveLayout L = solve_layout(P);
     // the thread's frame in shared memory ([thread][kPrepFrame] words, odd stride: conflict-free
