@@ -84,3 +84,21 @@ for k, v in prod.most_common(30):
 print("-- unattributed (waiting instruction)")
 for k, v in cons.most_common(10):
     print(k, v)
+# instruction and sample share per file / hottest lines (same attribution)
+inst, samp, thr = collections.Counter(), collections.Counter(), collections.Counter()
+for (ln, _), r in zip(lines, data):
+    n = int(r[ix["Instructions Executed"]] or 0)
+    inst[ln] += n
+    samp[ln] += int(r[ix["# Samples"]] or 0)
+    thr[ln] += int(r[ix["Thread Instructions Executed"]] or 0)
+ti, ts = sum(inst.values()), sum(samp.values())
+fi, fs = collections.Counter(), collections.Counter()
+for ln in inst:
+    fi[ln[0] if ln else None] += inst[ln]
+    fs[ln[0] if ln else None] += samp[ln]
+print("-- per file: inst%  samples%")
+for k, v in fi.most_common(14):
+    print(f"{str(k):28s} {100 * v / ti:5.1f} {100 * fs[k] / ts:5.1f}")
+print("-- hottest lines by samples: samples% inst% avg threads")
+for ln, v in samp.most_common(40):
+    print(f"{str(ln):34s} {100 * v / ts:5.1f} {100 * inst[ln] / ti:5.1f} {thr[ln] / max(inst[ln], 1):5.1f}")
