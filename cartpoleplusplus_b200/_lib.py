@@ -11,7 +11,21 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libbcp.so")
 
 EXPORTS = ["bcp_abi_version", "bcp_config_size", "bcp_last_error", "bcp_create", "bcp_destroy", "bcp_reset",
            "bcp_step", "bcp_rollout_random", "bcp_stats", "bcp_stats_clear", "bcp_get_state", "bcp_set_state",
-           "bcp_substep", "bcp_launch_count", "bcp_bench_fma_peak", "bcp_profile_begin", "bcp_profile_end", "bcp_last_solve_info"]
+           "bcp_substep", "bcp_launch_count", "bcp_bench_fma_peak", "bcp_profile_begin", "bcp_profile_end", "bcp_last_solve_info",
+           # include/bcp_replay.h
+           "bcp_replay_config_size", "bcp_replay_create", "bcp_replay_destroy", "bcp_replay_begin", "bcp_replay_observe",
+           "bcp_replay_add_episode", "bcp_replay_batch", "bcp_replay_info", "bcp_replay_export", "bcp_replay_launch_count"]
+
+REPLAY_ABI_VERSION = 1
+REPLAY_INFO_WORDS = 10
+REPLAY_ERR_UNDERFLOW, REPLAY_ERR_STAGING, REPLAY_ERR_INDEX, REPLAY_ERR_ROUNDS = 1, 2, 4, 8
+
+
+class BcpReplayConfig(ctypes.Structure):
+    """mirror of bcp_replay_config (include/bcp_replay.h)"""
+    _fields_ = [("abi_version", ctypes.c_int32), ("device_ordinal", ctypes.c_int32), ("buffer_size", ctypes.c_int64),
+                ("state_buffer_size", ctypes.c_int64), ("state_words", ctypes.c_int32), ("action_dim", ctypes.c_int32),
+                ("num_envs", ctypes.c_int32), ("max_episode_len", ctypes.c_int32)]
 
 
 class BcpError(RuntimeError):
@@ -50,10 +64,24 @@ def load(build_if_missing: bool = False):
     lib.bcp_profile_end.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     lib.bcp_last_solve_info.argtypes = [vp, vp, ctypes.c_size_t, vp]
     lib.bcp_launch_count.restype = ctypes.c_int64
+    i64, u64 = ctypes.c_int64, ctypes.c_uint64
+    lib.bcp_replay_config_size.restype = ctypes.c_size_t
+    lib.bcp_replay_create.argtypes = [ctypes.POINTER(BcpReplayConfig), ctypes.POINTER(vp)]
+    lib.bcp_replay_destroy.argtypes = [vp]
+    lib.bcp_replay_begin.argtypes = [vp, vp, vp, vp]
+    lib.bcp_replay_observe.argtypes = [vp, vp, i32, vp, vp, vp, vp, vp]
+    lib.bcp_replay_add_episode.argtypes = [vp, vp, vp, vp, vp, i32, vp]
+    lib.bcp_replay_batch.argtypes = [vp, vp, i32, u64, u64, vp, vp, vp, vp, vp, vp, vp]
+    lib.bcp_replay_info.argtypes = [vp, vp, vp]
+    lib.bcp_replay_export.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp]
+    lib.bcp_replay_launch_count.argtypes = [vp]
+    lib.bcp_replay_launch_count.restype = i64
     if lib.bcp_abi_version() != C.BCP_ABI_VERSION:
         raise BcpError(f"libbcp.so ABI {lib.bcp_abi_version()} != python mirror {C.BCP_ABI_VERSION}: rebuild")
     if lib.bcp_config_size() != ctypes.sizeof(C.BcpConfig):
         raise BcpError("sizeof(bcp_config) differs between libbcp.so and the ctypes mirror: rebuild")
+    if lib.bcp_replay_config_size() != ctypes.sizeof(BcpReplayConfig):
+        raise BcpError("sizeof(bcp_replay_config) differs between libbcp.so and the ctypes mirror: rebuild")
     _LIB = lib
     return lib
 

@@ -21,6 +21,7 @@ UNITS = [
     ("bcp_f32.cu", ["-prec-div=false", "-prec-sqrt=false", "-ftz=true"]),
     ("bcp_f64.cu", ["-fmad=false"]),
     ("bcp_abi.cu", []),
+    ("bcp_replay.cu", []),
 ]
 
 
@@ -32,8 +33,9 @@ def _nvcc() -> str:
 
 
 def _sources():
-    inc = os.path.join(CSRC, "..", "..", "include", "bcp.h")
-    return [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))] + [inc]
+    inc = os.path.join(CSRC, "..", "..", "include")
+    return [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh"))] + \
+        [os.path.join(inc, f) for f in os.listdir(inc) if f.endswith(".h")]
 
 
 def is_stale() -> bool:

@@ -32,6 +32,10 @@ int fail(const char* what, cudaError_t e = cudaSuccess) {
 
 }  // namespace
 
+namespace bcp {
+int abi_fail(const char* what, cudaError_t e) { return fail(what, e); }  // the other translation units' way to bcp_last_error()
+}
+
 struct bcp_env {
   bcp_config cfg;
   bcp::Params<float> p32;
