@@ -23,6 +23,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdlib>
 #include <new>
 #include <type_traits>
 
@@ -270,7 +271,8 @@ __global__ void __launch_bounds__(kPushT) k_rp_push2(View v, int round) {
     if (blockIdx.x == gridDim.x - 1) v.ctl[C_PB0 + ((round + 1) & 1)] = run;
   }
 }
-// one warp per finished episode: rows of the ring, states into the pool
+// one warp per 32 consecutive transitions of the pass: rows of the ring, states into the pool.
+// A lane finds its episode by bisection over the episodes' transition offsets.
 template <bool EVEN>
 __global__ void __launch_bounds__(256) k_rp_pop(View v, int round) {
   const unsigned FULL = 0xffffffffu;
@@ -284,50 +286,55 @@ __global__ void __launch_bounds__(256) k_rp_pop(View v, int round) {
   typedef typename std::conditional<EVEN, uint32_t, unsigned short>::type G;
   G* const pool = reinterpret_cast<G*>(v.state);
   const i64 warps = (i64)gridDim.x * (blockDim.x >> 5);
-  for (i64 k = (i64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); k < K; k += warps) {
-    const int slot = v.ep_slot[k], len = v.ep_len[k];
-    const i64 O = v.ep_off[k];
-    if (O >= r1 || O + len <= r0) continue;
-    const float* sa = slot_action(v, slot);
-    const float* sr = slot_reward(v, slot);
-    for (int nb = 0; nb < len; nb += 32) {
-      const int n = nb + lane;
-      const i64 g = O + n;
-      const bool act = n < len && g >= r0 && g < r1;
-      if (!__any_sync(FULL, act)) continue;
-      int s1 = 0, s2 = 0;
-      if (act) {
-        const i64 a2 = head + k + 1 + g;  // pops before this one: k + 1 initial states, g state_2s
-        const i64 i = g - r0;
-        const i64 pushed = v.pushcum[i];
-        const i64 pushed_before = n == 0 ? (i > 0 ? (i64)v.pushcum[i - 1] : pb) : pushed;  // initial-state pop precedes g's pushes
-        if (a2 >= tail + pushed || a2 - 1 >= tail + pushed_before) atomicOr((u64*)&v.ctl[C_ERROR], (u64)BCP_REPLAY_ERR_UNDERFLOW);
-        s2 = v.fq[a2 % v.C];
-        s1 = v.fq[(a2 - 1) % v.C];
-        const i64 pos = (insert0 + g) % v.N;
-        v.s1_idx[pos] = s1;  // :96-107
-        v.s2_idx[pos] = s2;
-        for (int a = 0; a < v.A; ++a) v.action[pos * v.A + a] = sa[(size_t)n * v.A + a];
-        v.reward[pos] = sr[n];
-        v.mask[pos] = (n == len - 1) ? 0.0f : 1.0f;  // :102
+  for (i64 g0 = r0 + 32 * ((i64)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)); g0 < r1; g0 += 32 * warps) {
+    const i64 g = g0 + lane;
+    const bool act = g < r1;
+    int s1 = 0, s2 = 0, n = 1;
+    const G* src = nullptr;   // the transition's state_2 row in the staging area
+    const G* src0 = nullptr;  // the episode's initial state (first transition only)
+    if (act) {
+      i64 lo = 0, hi = K;  // last episode with ep_off <= g
+      while (hi - lo > 1) {
+        const i64 mid = (lo + hi) >> 1;
+        if (v.ep_off[mid] <= g) lo = mid; else hi = mid;
       }
-      // states: the chunk's 32 state_2 rows are contiguous in the staging area
-      const G* src = reinterpret_cast<const G*>(slot_state(v, slot, (i64)nb + 1));
-      for (int base = 0; base < 32 * Wc; base += 32) {
-        const int idx = base + lane;
-        const int j = idx / Wc, w = idx - j * Wc;
-        const int s2j = __shfl_sync(FULL, s2, j & 31);
-        const bool aj = __shfl_sync(FULL, (int)act, j & 31) != 0;
-        if (aj) pool[(size_t)s2j * Wc + w] = src[idx];
-      }
-      if (nb == 0) {  // the episode's initial state (:66-67)
-        const int s10 = __shfl_sync(FULL, s1, 0);
-        const bool a0 = __shfl_sync(FULL, (int)act, 0) != 0;
-        if (a0) {
-          const G* s0 = reinterpret_cast<const G*>(slot_state(v, slot, 0));
-          for (int w = lane; w < Wc; w += 32) pool[(size_t)s10 * Wc + w] = s0[w];
-        }
-      }
+      const i64 k = lo;
+      const int slot = v.ep_slot[k], len = v.ep_len[k];
+      n = (int)(g - v.ep_off[k]);
+      const i64 a2 = head + k + 1 + g;  // pops before this one: k + 1 initial states, g state_2s
+      const i64 i = g - r0;
+      const i64 pushed = v.pushcum[i];
+      const i64 pushed_before = n == 0 ? (i > 0 ? (i64)v.pushcum[i - 1] : pb) : pushed;  // the initial-state pop precedes g's pushes
+      if (a2 >= tail + pushed || a2 - 1 >= tail + pushed_before) atomicOr((u64*)&v.ctl[C_ERROR], (u64)BCP_REPLAY_ERR_UNDERFLOW);
+      s2 = v.fq[a2 % v.C];
+      s1 = v.fq[(a2 - 1) % v.C];
+      const i64 pos = (insert0 + g) % v.N;
+      v.s1_idx[pos] = s1;  // :96-107
+      v.s2_idx[pos] = s2;
+      const float* sa = slot_action(v, slot) + (size_t)n * v.A;
+      for (int a = 0; a < v.A; ++a) v.action[pos * v.A + a] = sa[a];
+      v.reward[pos] = slot_reward(v, slot)[n];
+      v.mask[pos] = (n == len - 1) ? 0.0f : 1.0f;  // :102
+      src = reinterpret_cast<const G*>(slot_state(v, slot, (i64)n + 1));
+      if (n == 0) src0 = reinterpret_cast<const G*>(slot_state(v, slot, 0));
+    }
+    // states: granule idx of the warp's 32 rows is copied by lane idx % 32
+    const u64 srcb = (u64)src;
+#pragma unroll 2
+    for (int base = 0; base < 32 * Wc; base += 32) {
+      const int idx = base + lane;
+      const int j = idx / Wc, w = idx - j * Wc;
+      const int s2j = __shfl_sync(FULL, s2, j & 31);
+      const G* sj = (const G*)__shfl_sync(FULL, srcb, j & 31);
+      if (sj) pool[(size_t)s2j * Wc + w] = sj[w];
+    }
+    unsigned firsts = __ballot_sync(FULL, src0 != nullptr);  // episodes that start in this chunk (:66-67)
+    while (firsts) {
+      const int j = __ffs(firsts) - 1;
+      firsts &= firsts - 1;
+      const int s1j = __shfl_sync(FULL, s1, j);
+      const G* s0 = (const G*)__shfl_sync(FULL, (u64)src0, j);
+      for (int w = lane; w < Wc; w += 32) pool[(size_t)s1j * Wc + w] = s0[w];
     }
   }
 }
@@ -427,6 +434,12 @@ struct bcp_replay {
   int scratch_cap = 0;
   int sms = 0;
   int64_t launches = 0;
+  // bcp_replay_observe as one CUDA graph launch: the call's kernels with their arguments, captured
+  // the first time a set of caller buffers is seen (an env loop passes the same buffers every call)
+  cudaGraphExec_t graph = nullptr;
+  cudaStream_t cap_stream = nullptr;
+  const void* graph_key[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+  int graph_act_i32 = 0, graph_nodes = 0, use_graph = 1;
 };
 
 namespace {
@@ -436,6 +449,7 @@ int grow_scratch(bcp_replay* rp, int n) {
   int cap = rp->scratch_cap ? rp->scratch_cap : 256;
   while (cap < n) cap *= 2;
   RCK(cudaDeviceSynchronize());  // earlier commits may still read the old scratch
+  if (rp->graph) { cudaGraphExecDestroy(rp->graph); rp->graph = nullptr; }  // the graph's kernels carry the old pointers
   cudaFree(rp->v.sc_state); cudaFree(rp->v.sc_action); cudaFree(rp->v.sc_reward); cudaFree(rp->in_states);
   rp->v.sc_state = nullptr; rp->v.sc_action = nullptr; rp->v.sc_reward = nullptr; rp->in_states = nullptr;
   rp->scratch_cap = 0;
@@ -474,7 +488,7 @@ int commit(bcp_replay* rp, const Feed& f, i64 max_T, cudaStream_t s) {
   int g_push = (int)((per_round + 4 * kPushT - 1) / (4 * kPushT));  // >= 4 tiles per block, at most 4 blocks per SM
   if (g_push > rp->sms * 4) g_push = rp->sms * 4;
   if (g_push < 1) g_push = 1;
-  int g_pop = (int)((((i64)slots < max_T ? (i64)slots : max_T) + 7) / 8);  // a warp per episode
+  int g_pop = (int)((per_round + 255) / 256);  // a warp per 32 transitions
   if (g_pop > rp->sms * 8) g_pop = rp->sms * 8;
   if (g_pop < 1) g_pop = 1;
   for (int r = 0; r < rounds; ++r) {
@@ -514,6 +528,7 @@ int bcp_replay_create(const bcp_replay_config* c, bcp_replay** out) {
   rp->cfg = *c;
   DeviceGuard g(c->device_ordinal);
   cudaDeviceGetAttribute(&rp->sms, cudaDevAttrMultiProcessorCount, c->device_ordinal);
+  if (const char* e2 = getenv("BCP_REPLAY_GRAPH")) rp->use_graph = atoi(e2) != 0;  // 0: plain launches (per-kernel profiling)
   View& v = rp->v;
   v = View{};
   v.N = c->buffer_size; v.M = c->state_buffer_size; v.C = v.M + 2 * v.N + 8;
@@ -551,6 +566,8 @@ int bcp_replay_destroy(bcp_replay* rp) {
   if (!rp) return 0;
   DeviceGuard g(rp->cfg.device_ordinal);
   cudaDeviceSynchronize();
+  if (rp->graph) cudaGraphExecDestroy(rp->graph);
+  if (rp->cap_stream) cudaStreamDestroy(rp->cap_stream);
   cudaFree(rp->arena);
   cudaFree(rp->v.sc_state); cudaFree(rp->v.sc_action); cudaFree(rp->v.sc_reward); cudaFree(rp->in_states);
   delete rp;
@@ -578,8 +595,36 @@ int bcp_replay_observe(bcp_replay* rp, const void* actions, int32_t actions_are_
   if (actions_are_int32 && rp->v.A != 1) return abi_fail("bcp_replay_observe: int32 actions need action_dim = 1", cudaSuccess);
   DeviceGuard g(rp->cfg.device_ordinal);
   const Feed f{actions, obs, reward, done, reason, nullptr, actions_are_int32, 0};
-  if (launch_states(rp, f, (cudaStream_t)stream)) return -1;
-  return commit(rp, f, (i64)rp->v.B * rp->v.L, (cudaStream_t)stream);
+  const i64 max_T = (i64)rp->v.B * rp->v.L;
+  if (!rp->use_graph) {
+    if (launch_states(rp, f, (cudaStream_t)stream)) return -1;
+    return commit(rp, f, max_T, (cudaStream_t)stream);
+  }
+  const void* key[6] = {actions, obs, reward, done, reason, nullptr};
+  bool same = rp->graph != nullptr && rp->graph_act_i32 == actions_are_int32;
+  for (int i = 0; i < 6 && same; ++i) same = key[i] == rp->graph_key[i];
+  if (!same) {
+    if (rp->graph) { cudaGraphExecDestroy(rp->graph); rp->graph = nullptr; }
+    if (!rp->cap_stream) RCK(cudaStreamCreateWithFlags(&rp->cap_stream, cudaStreamNonBlocking));
+    const int64_t before = rp->launches;
+    RCK(cudaStreamBeginCapture(rp->cap_stream, cudaStreamCaptureModeThreadLocal));
+    int rc = launch_states(rp, f, rp->cap_stream);
+    if (!rc) rc = commit(rp, f, max_T, rp->cap_stream);
+    cudaGraph_t g = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(rp->cap_stream, &g);
+    rp->graph_nodes = (int)(rp->launches - before);
+    rp->launches = before;
+    if (rc) { if (g) cudaGraphDestroy(g); return -1; }
+    if (ce != cudaSuccess) return abi_fail("bcp_replay_observe: stream capture", ce);
+    const cudaError_t ie = cudaGraphInstantiate(&rp->graph, g, 0);
+    cudaGraphDestroy(g);
+    if (ie != cudaSuccess) { rp->graph = nullptr; return abi_fail("bcp_replay_observe: cudaGraphInstantiate", ie); }
+    for (int i = 0; i < 6; ++i) rp->graph_key[i] = key[i];
+    rp->graph_act_i32 = actions_are_int32;
+  }
+  RCK(cudaGraphLaunch(rp->graph, (cudaStream_t)stream));
+  rp->launches += rp->graph_nodes;
+  return 0;
 }
 
 int bcp_replay_add_episode(bcp_replay* rp, const float* initial_state, const float* actions, const float* rewards,

@@ -68,11 +68,22 @@ class DeviceReplayMemory:
         except Exception:
             pass
 
+    def _u8(self, x):
+        if type(x) is torch.Tensor and x.is_cuda and x.is_contiguous():
+            if x.dtype == torch.uint8:
+                return x
+            if x.dtype == torch.bool:
+                return x.view(torch.uint8)  # 0/1 bytes: a view, no kernel
+        return torch.as_tensor(x, device=self.device).to(torch.uint8).contiguous()
+
     def _stream(self):
         return ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
 
     def _f32(self, x, shape):
-        t = torch.as_tensor(x, dtype=torch.float32, device=self.device).contiguous()
+        if type(x) is torch.Tensor and x.dtype == torch.float32 and x.is_cuda and x.is_contiguous():
+            t = x  # the env's own output buffers: nothing to convert
+        else:
+            t = torch.as_tensor(x, dtype=torch.float32, device=self.device).contiguous()
         if t.numel() != int(np.prod(shape)):
             raise ValueError(f"expected {shape}, got {tuple(t.shape)}")
         return t
@@ -81,22 +92,24 @@ class DeviceReplayMemory:
     def begin(self, obs, mask=None):
         """After env.reset(): obs[e] is the initial state of a new episode of env e (every env, or where mask)."""
         o = self._f32(obs, (self.num_envs,) + self.state_shape)
-        m = None if mask is None else torch.as_tensor(mask, device=self.device).to(torch.uint8).contiguous()
+        m = None if mask is None else self._u8(mask)
         _lib.check(self._lib.bcp_replay_begin(self._h, _p(o), _p(m), self._stream()), self._lib)
 
     def observe(self, actions, obs, reward, done, reason=None):
         """After env.step(actions) -> (obs, reward, done, info): stage one transition per open episode
         and add every episode that finished (env-id order).  `reason` = info['done_reason'] of a
         pipelined auto-reset env (codes 4 / 5 are not transitions)."""
-        a = torch.as_tensor(actions, device=self.device)
+        a = actions if type(actions) is torch.Tensor and actions.is_cuda else torch.as_tensor(actions, device=self.device)
         is_int = not a.dtype.is_floating_point
-        a = a.to(torch.int32 if is_int else torch.float32).contiguous()
+        want = torch.int32 if is_int else torch.float32
+        if a.dtype != want or not a.is_contiguous():
+            a = a.to(want).contiguous()
         if a.numel() != self.num_envs * (1 if is_int else self.action_dim):
             raise ValueError(f"actions: got {tuple(a.shape)} for {self.num_envs} envs, action_dim {self.action_dim}")
         o = self._f32(obs, (self.num_envs,) + self.state_shape)
         r = self._f32(reward, (self.num_envs,))
-        d = torch.as_tensor(done, device=self.device).to(torch.uint8).contiguous()
-        rs = None if reason is None else torch.as_tensor(reason, device=self.device).to(torch.uint8).contiguous()
+        d = self._u8(done)
+        rs = None if reason is None else self._u8(reason)
         _lib.check(self._lib.bcp_replay_observe(self._h, _p(a), 1 if is_int else 0, _p(o), _p(r), _p(d), _p(rs), self._stream()),
                    self._lib)
 
