@@ -189,3 +189,40 @@ def test_env_rollout_into_replay(built):
         np.testing.assert_array_equal(x.cpu().numpy().reshape(y.shape), y)
     env.close()
     dev.close()
+
+
+def test_event_log_round_trip_into_replay(built, tmp_path):
+    """env rollout -> BatchedEventLog file -> DeviceReplayMemory.reset_from_event_log (replay_memory.py:43-62)
+    == the oracle fed the same episodes; the file also parses as the reference's format."""
+    from cartpoleplusplus_b200 import default_opts
+    from cartpoleplusplus_b200 import event_log as el
+    from cartpoleplusplus_b200.env import BatchedBulletCartpole
+    from oracle.replay_oracle import ReplayMemoryOracle
+    B = 64
+    opts = default_opts(action_force=100.0, max_episode_len=9, auto_reset="pipelined")
+    env = BatchedBulletCartpole(opts, discrete_actions=False, num_envs=B, device=0, dtype="fp32", seed=2)
+    path = str(tmp_path / "events.bin")
+    log = el.BatchedEventLog(path, B)
+    obs = env.reset()
+    log.begin(obs.cpu().numpy())
+    g = torch.Generator(device="cuda").manual_seed(1)
+    for _ in range(90):
+        a = torch.rand((B, 2), device="cuda", generator=g) * 2 - 1
+        obs, rew, done, info = env.step(a)
+        log.observe(a.cpu().numpy(), obs.cpu().numpy(), rew.cpu().numpy(), done.cpu().numpy(), info["done_reason"].cpu().numpy())
+    log.close()
+    env.close()
+    assert log.episodes_written >= B
+    dev = _mem(buffer_size=400, state_shape=(2, 2, 7), action_dim=2)
+    n_eps, n_events = dev.reset_from_event_log(path)
+    ora = ReplayMemoryOracle(400, (2, 2, 7), 2)
+    k = 0
+    for ep in el.EventLogReader(path).entries():
+        seq = [(np.float32(ev.action), ev.reward, el.read_state_from_event(ev)) for ev in ep.event[1:]]
+        ora.add_episode(el.read_state_from_event(ep.event[0]), seq)
+        k += 1
+        if ora.full:
+            break
+    assert k == n_eps and ora.full and dev.full
+    assert_same(dev, ora)
+    dev.close()
