@@ -48,7 +48,7 @@ struct bcp_env {
   int* list = nullptr;   // compacted env indices for masked resets
   int* count = nullptr;
   double* staging = nullptr;  // canonical records for get/set_state
-  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1};  // solve records / queue of the split pipeline
+  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
   int use_split = 0;
   bool profiling = false;
   std::vector<cudaEvent_t> prof_events;  // bracketing every kernel of bcp_step while profiling
@@ -138,8 +138,10 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
     if (cfg->manifold_order != 0 || cfg->friction_dirs != 2 || !cfg->cone_friction) h->use_split = 0;
     if (h->use_split) {
       A((void**)&h->split.recs, bcp::split_record_words(h->p32) * N * sizeof(float));
-      A((void**)&h->split.queue, N * 2 * sizeof(int));  // {env, contact counts} per entry
+      A((void**)&h->split.queue, N * 4 * sizeof(int));  // {env, contact counts} per entry; main queue, then the generic one
       A((void**)&h->split.qc, bcp::split_counter_words(h->p32) * sizeof(int));
+      A((void**)&h->split.cont, bcp::split_cont_words(h->p32) * sizeof(float));
+      A((void**)&h->split.contm, N * 4 * sizeof(int));
       for (int k = 0; k < 2; ++k) {
         A((void**)&h->split.bins[k], bcp::split_bins_words(h->p32) * sizeof(int));
         A((void**)&h->split.cnts[k], 8 * sizeof(int));
@@ -159,7 +161,8 @@ int bcp_destroy(bcp_env* h) {
   DeviceGuard g(h->cfg.device_ordinal);
   cudaFree(h->fdata); cudaFree(h->idata); cudaFree(h->hist); cudaFree(h->header);
   cudaFree(h->reward_sum); cudaFree(h->list); cudaFree(h->count); cudaFree(h->staging);
-  cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc);
+  if (h->split.side) { cudaStreamDestroy(h->split.side); cudaEventDestroy(h->split.ev_prep); cudaEventDestroy(h->split.ev_gen); }
+  cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc); cudaFree(h->split.cont); cudaFree(h->split.contm);
   for (int k = 0; k < 2; ++k) { cudaFree(h->split.bins[k]); cudaFree(h->split.cnts[k]); }
   delete h;
   return 0;

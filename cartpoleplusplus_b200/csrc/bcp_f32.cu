@@ -6,7 +6,8 @@ namespace bcp {
 template struct Launch<float>;
 
 size_t split_record_words(const Params<float>& P) { return (size_t)record_words(P); }
-size_t split_counter_words(const Params<float>& P) { return (size_t)(P.R * P.S) * Q_WORDS; }
+size_t split_counter_words(const Params<float>& P) { return (size_t)(P.R * P.S) * 3 * Q_WORDS; }  // main queue, generic queue, continuation counts
+size_t split_cont_words(const Params<float>& P) { return (size_t)LAM_WORDS * (size_t)P.num_envs; }
 size_t split_bins_words(const Params<float>& P) { return (size_t)N_BINS * (size_t)P.num_envs; }
 
 template <bool FRICTION>
@@ -39,6 +40,44 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   L.smem = (size_t)col_stride * L.block * sizeof(float);
   err = allow_smem(k_solve<float, FRICTION>, L.smem);
   if (err != cudaSuccess) return err;
+  err = allow_smem(k_solve_lam<float, FRICTION>, L.smem);
+  if (err != cudaSuccess) return err;
+  // Impulse-space solver (bcp_lambda.cuh) on the main queue.  It shortens the dependent chain of an
+  // iteration, which is what bounds the solve phase while a launch is about one wave of envs
+  // (measured on B200: +6..7 % env-steps/s at 32 768 and 65 536 envs, equal at 131 072); beyond
+  // that the phase is issue-bound and building the matrices costs more than it saves (-3 % at
+  // 262 144, -8 % at 1 M).  BCP_LAMBDA=1 / 0 forces it on / off.
+  static int lam_env = -2;
+  if (lam_env == -2) {
+    const char* le = getenv("BCP_LAMBDA");
+    lam_env = le ? atoi(le) : -1;
+  }
+  const bool lam_wanted = lam_env < 0 ? N < 131072 : lam_env != 0;
+  const int use_lam = (lam_wanted && lam_config_ok(P) && b.cont) ? 1 : 0;
+  static int handoff = -1;
+  if (handoff < 0) {
+    const char* he = getenv("BCP_HANDOFF");
+    handoff = he ? atoi(he) : 8;  // iterations after which a solve moves to k_solve_tail (0: never)
+  }
+  int tail_grid = (N + kBlock - 1) / kBlock;
+  if (tail_grid > 2 * 148) tail_grid = 2 * 148;
+  static int side_env = -1;
+  if (side_env < 0) {
+    const char* se = getenv("BCP_SIDE");
+    side_env = se ? atoi(se) : 1;
+  }
+  // The few envs of the generic queue (pole touching cart AND ground) still solve row by row, and one
+  // that needs all 50 iterations takes as long as the whole impulse-space phase: their k_solve gets
+  // a handful of blocks on a high-priority side stream and runs beside k_solve_lam / k_solve_tail.
+  const bool side = use_lam && side_env;
+  if (side && !b.side) {
+    int lo = 0, hi = 0;
+    cudaDeviceGetStreamPriorityRange(&lo, &hi);
+    err = cudaStreamCreateWithPriority(&b.side, cudaStreamNonBlocking, hi);
+    if (err != cudaSuccess) return err;
+    cudaEventCreateWithFlags(&b.ev_prep, cudaEventDisableTiming);
+    cudaEventCreateWithFlags(&b.ev_gen, cudaEventDisableTiming);
+  }
   static int sms = 0, per_sm = 0;
   static size_t per_sm_smem = (size_t)-1;
   if (!sms || per_sm_smem != L.smem) {
@@ -58,6 +97,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
     if (fetch_min > 32) fetch_min = 32;
   }
   const int solve_grid = min(sms * per_sm, (N + L.block - 1) / L.block);
+  const int gen_grid = side ? min(solve_grid, 16) : solve_grid;
   static int prep_block = 0;
   if (!prep_block) {
     const char* pb = getenv("BCP_PREP_BLOCK");
@@ -71,12 +111,30 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   mark();
   for (int k = 0; k <= RS; ++k) {
     const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
-    int* qc = b.qc + (size_t)(k < RS ? k : 0) * Q_WORDS;
-    k_prep<float, FRICTION><<<prep_grid, prep_block, prep_smem, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set);
+    int* qc = b.qc + (size_t)(k < RS ? k : 0) * 3 * Q_WORDS;
+    k_prep<float, FRICTION><<<prep_grid, prep_block, prep_smem, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set, use_lam);
     if (launches) ++*launches;
     mark();
     if (k < RS) {
-      k_solve<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc, col_stride, fetch_min);
+      if (use_lam) {
+        if (side) {
+          cudaEventRecord(b.ev_prep, s);
+          cudaStreamWaitEvent(b.side, b.ev_prep, 0);
+          k_solve<float, FRICTION><<<gen_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride, fetch_min);
+          cudaEventRecord(b.ev_gen, b.side);
+        }
+        k_solve_lam<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc, col_stride, fetch_min,
+                                                                          b.cont, reinterpret_cast<int4*>(b.contm), handoff);
+        if (handoff > 0) {
+          k_solve_tail<float, FRICTION><<<tail_grid, kBlock, 0, s>>>(P, b.recs, rec_words, qc, b.cont, reinterpret_cast<const int4*>(b.contm));
+          if (launches) ++*launches;
+        }
+        if (side) cudaStreamWaitEvent(s, b.ev_gen, 0);  // the next k_prep finishes these envs too
+        else k_solve<float, FRICTION><<<gen_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride, fetch_min);
+        if (launches) ++*launches;
+      } else {
+        k_solve<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc, col_stride, fetch_min);
+      }
       if (launches) ++*launches;
       mark();
     }

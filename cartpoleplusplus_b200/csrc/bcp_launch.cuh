@@ -37,7 +37,13 @@ struct SplitBuffers {
   int* bins[2];  // visiting order, double buffered: [8][num_envs] env ids each
   int* cnts[2];  // [8] each
   int cur;       // which of the two the next call reads; -1: no order yet (identity)
+  float* cont;   // continuation buffer of the impulse-space solver: [LAM_WORDS][num_envs]
+  int* contm;    // int4 per slot: env, iterations so far, contact counts, regime
+  // the generic queue's k_solve runs beside the impulse-space kernels on a high-priority side stream
+  cudaStream_t side;
+  cudaEvent_t ev_prep, ev_gen;
 };
+size_t split_cont_words(const Params<float>& P);
 size_t split_bins_words(const Params<float>& P);
 size_t split_record_words(const Params<float>& P);
 size_t split_counter_words(const Params<float>& P);

@@ -18,7 +18,7 @@
 // rows are the same rows in the solver's 16-byte format (bcp_solve.cuh).
 #pragma once
 #include <cstring>
-#include "bcp_solve.cuh"
+#include "bcp_lambda.cuh"
 #include "bcp_state.cuh"
 
 namespace bcp {
@@ -209,10 +209,26 @@ BCP_HD void substep_split_reference(const Params<T>& P, Env<T>& st, T* rec, Subs
   solve_consts(P, R, S);
   solve_load(rec, S, cnt, R);
   int it = 0;
-  for (int k = 0; k < P.solver_iterations; ++k) {
-    const T lsr = solve_iteration<T, FRICTION>(P, rec + REC_ROWS, L, cnt, R);
-    it = k + 1;
-    if (lsr <= P.residual_thr || k >= P.solver_iterations - 1) break;
+  const int lmode = lam_config_ok(P) ? lam_mode_of(cnt[0], cnt[1], cnt[2]) : (int)LAM_NONE;
+  if (lmode != LAM_NONE && !getenv("BCP_NO_LAMBDA")) {  // the impulse-space iteration of k_solve_lam (bcp_lambda.cuh)
+    LamSys<T> Sy;
+    const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+    if (lmode == LAM_STACK) lam_build_stack<false>(P, rec + REC_ROWS, L, R.apn, Sy);
+    else lam_build_split<false, FRICTION>(P, rec + REC_ROWS, L, R.apn, Sy);
+    for (int k = 0; k < P.solver_iterations; ++k) {
+      const T lsr = lmode == LAM_STACK ? lam_round_stack(P, cnt[BCP_PAIR_CART_POLE], cnt[BCP_PAIR_GROUND_CART], Sy)
+                                       : lam_round_split<FRICTION>(P, fr, cnt[BCP_PAIR_GROUND_POLE], cnt[BCP_PAIR_GROUND_CART], Sy);
+      it = k + 1;
+      if (lsr <= P.residual_thr || k >= P.solver_iterations - 1) break;
+    }
+    if (lmode == LAM_STACK) lam_finish_stack<false>(P, rec + REC_ROWS, L, Sy, R);
+    else lam_finish_split<false, FRICTION>(P, rec + REC_ROWS, L, Sy, R);
+  } else {
+    for (int k = 0; k < P.solver_iterations; ++k) {
+      const T lsr = solve_iteration<T, FRICTION>(P, rec + REC_ROWS, L, cnt, R);
+      it = k + 1;
+      if (lsr <= P.residual_thr || k >= P.solver_iterations - 1) break;
+    }
   }
   solve_end(rec, S, it, R);
   split_finish(P, st, rec);
@@ -289,7 +305,7 @@ template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
                                                  int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
-                                                 int s_set) {
+                                                 int s_set, int use_lam) {
   const int N = P.num_envs;
   const int e_visit = visit(vo, blockIdx.x * blockDim.x + threadIdx.x, N);
   const bool valid = e_visit >= 0;
@@ -383,20 +399,28 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     BCP_WARP_SYNC();
     if (on) setup_end(P, st, C, rec);
     // queue the env: one atomic per warp and bin
-    const bool is_long = on && last_iters >= kLongIters;
-    const unsigned ml = __ballot_sync(0xffffffffu, is_long), ms = __ballot_sync(0xffffffffu, on && !is_long);
+    // with the impulse-space solver on the main queue, an env in a regime it does not cover goes to
+    // the generic queue (second half of `queue`, second counter block)
+    const bool generic = on && use_lam &&
+        lam_mode_of(st.mani[BCP_PAIR_GROUND_CART].count, st.mani[BCP_PAIR_CART_POLE].count, st.mani[BCP_PAIR_GROUND_POLE].count) == LAM_NONE;
+    const bool is_long = on && !generic && last_iters >= kLongIters;
+    const unsigned ml = __ballot_sync(0xffffffffu, is_long), ms = __ballot_sync(0xffffffffu, on && !is_long && !generic);
+    const unsigned mg = __ballot_sync(0xffffffffu, generic);
     const int lane = threadIdx.x & 31;
-    int bl = 0, bs = 0;
+    int bl = 0, bs = 0, bg = 0;
     if (lane == 0) {
       if (ml) bl = atomicAdd(&qc_set[Q_LONG], __popc(ml));
       if (ms) bs = atomicAdd(&qc_set[Q_SHORT], __popc(ms));
+      if (mg) bg = atomicAdd(&qc_set[Q_WORDS + Q_SHORT], __popc(mg));
     }
     bl = __shfl_sync(0xffffffffu, bl, 0);
     bs = __shfl_sync(0xffffffffu, bs, 0);
+    bg = __shfl_sync(0xffffffffu, bg, 0);
     const unsigned lt = (1u << lane) - 1;
     // entry = env id + its three contact counts (the solver sizes its copy without the record)
     const int2 entry = make_int2(e, queue_meta(st));
     if (is_long) queue[bl + __popc(ml & lt)] = entry;
+    else if (generic) queue[N + N - 1 - (bg + __popc(mg & lt))] = entry;
     else if (on) queue[N - 1 - (bs + __popc(ms & lt))] = entry;
   } else {  // the call closes: steps / done / reward (:239-260), outputs, episode statistics
     if (fin) for (int m = 0; m < 3; ++m) finish_impulses(f, e, m, st.mani[m].count, fin_apn);
@@ -571,6 +595,228 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
       const bool still = (busy_m >> lane) & 1u;
 #pragma unroll
       for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, still ? cnt[m] : 0);
+    }
+  }
+}
+// k_solve in impulse space (bcp_lambda.cuh): same queue, same staged record -> column copies, same
+// retire-and-refill; a lane builds its env's Delassus matrix when it starts the env and iterates on
+// registers.  Serves the envs k_prep queued on the main queue when the configuration allows it
+// (lam_config_ok); envs in a regime it does not cover go to the generic queue and k_solve.
+template <typename T, bool FRICTION>
+__global__ void __launch_bounds__(kBlock, 2) k_solve_lam(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
+                                                  const int2* __restrict__ queue, int* __restrict__ qc, int col_stride,
+                                                  int fetch_min, T* __restrict__ cont, int4* __restrict__ contm, int handoff_it) {
+  const unsigned FULL = 0xffffffffu;
+  T* const smem = reinterpret_cast<T*>(bcp_smem);
+  const int lane = threadIdx.x & 31, warp_base = threadIdx.x - lane;
+  T* const col = smem + (size_t)threadIdx.x * col_stride;
+  const SolveLayout L = solve_layout(P);
+  const int N = P.num_envs;
+  const int n_long = qc[Q_LONG], total = n_long + qc[Q_SHORT];
+  const unsigned lt = (1u << lane) - 1;
+  const int rec16 = (rec_words * (int)sizeof(T)) >> 4, hdr16 = (REC_ROWS * (int)sizeof(T)) >> 4;
+  // The record -> column copy: this lane moves the 16-byte pieces lane, lane + 32, ... of every
+  // record its warp takes.  What block a piece lies in never changes, so it is worked out once:
+  // piece k is live iff  pc_off[k] < count(pair pc_shift[k] / 8) * pc_per[k]   (header: always).
+  int pc_shift[kMaxPieces], pc_off[kMaxPieces], pc_per[kMaxPieces];
+#pragma unroll
+  for (int k = 0; k < kMaxPieces; ++k) {
+    const int i = lane + 32 * k;
+    pc_shift[k] = 0; pc_off[k] = (i < hdr16) ? -1 : 0x7fffffff; pc_per[k] = 0;  // header piece / outside every block
+#pragma unroll
+    for (int m = 0; m < 3; ++m) {
+      const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
+      const int lo = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4, per = (w * (int)sizeof(T)) >> 4;
+      if (i >= lo && i < lo + 4 * per) { pc_shift[k] = 8 * m; pc_off[k] = i - lo; pc_per[k] = per; }
+      if (L.fbase[m] >= 0) {
+        const int flo = ((REC_ROWS + L.fbase[m]) * (int)sizeof(T)) >> 4, fper = ((L.rpc[m] - 1) * w * (int)sizeof(T)) >> 4;
+        if (i >= flo && i < flo + 4 * fper) { pc_shift[k] = 8 * m; pc_off[k] = i - flo; pc_per[k] = fper; }
+      }
+    }
+  }
+  int w_next = 0, w_end = 0;  // the warp's slice of the queue (uniform)
+  bool exhausted = total == 0;
+  SolveScale<T> S;
+  {
+    SolveRegs<T> R0;
+    solve_consts(P, R0, S);
+  }
+  LamSys<T> Sy;  // the lane's env in impulse space (bcp_lambda.cuh)
+  int lmode = LAM_NONE;
+  const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+  int cnt[3] = {0, 0, 0}, mx[3] = {0, 0, 0};
+  int it = 0;
+  T* rec = nullptr;
+  unsigned busy_m = 0, staged_m = 0;  // lanes iterating / lanes whose copy is in flight (warp-uniform)
+  const T res_thr = P.residual_thr;
+  const int max_it = P.solver_iterations;
+  while (true) {
+    if (staged_m) {  // copies issued one iteration ago: start those lanes
+      cp_async_wait_all();
+      __syncwarp();
+      if ((staged_m >> lane) & 1u) {
+        SolveRegs<T> R;
+        solve_load(col, S, cnt, R);  // counts and warm-start impulses
+        lmode = lam_mode_of(cnt[0], cnt[1], cnt[2]);
+        if (lmode == LAM_STACK) lam_build_stack<true>(P, col + REC_ROWS, L, R.apn, Sy);
+        else lam_build_split<true, FRICTION>(P, col + REC_ROWS, L, R.apn, Sy);
+        it = 0;
+      }
+      busy_m |= staged_m;
+      staged_m = 0;
+      const bool busy = (busy_m >> lane) & 1u;
+#pragma unroll
+      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
+    }
+    const unsigned idle = ~busy_m;
+    if (idle && !exhausted && (idle == FULL || __popc(idle) >= fetch_min)) {
+      unsigned need = idle;
+      int idx = -1;
+      while (need && !exhausted) {
+        const int avail = w_end - w_next;
+        const int rank = __popc(need & lt);
+        const bool mine = ((need >> lane) & 1u) && rank < avail;
+        if (mine) idx = w_next + rank;
+        const unsigned got = __ballot_sync(FULL, mine);
+        need &= ~got;
+        w_next += __popc(got);
+        if (!need) break;
+        int b = 0;
+        if (lane == 0) b = atomicAdd(&qc[Q_FETCH], kFetchChunk);
+        b = __shfl_sync(FULL, b, 0);
+        if (b >= total) exhausted = true;
+        else { w_next = b; w_end = min(b + kFetchChunk, total); }
+      }
+      int env = -1, meta = 0;
+      if (idx >= 0) {
+        const int2 q = queue[idx < n_long ? idx : N - 1 - (idx - n_long)];
+        env = q.x;
+        meta = q.y;
+        rec = recs + (size_t)env * rec_words;
+      }
+      staged_m = __ballot_sync(FULL, idx >= 0);
+      unsigned taken = staged_m;
+      while (taken) {
+        const int src = __ffs(taken) - 1;
+        taken &= taken - 1;
+        const int e_src = __shfl_sync(FULL, env, src), m_src = __shfl_sync(FULL, meta, src);
+        const char* r_src = reinterpret_cast<const char*>(recs + (size_t)e_src * rec_words) + 16 * lane;
+        char* c_dst = reinterpret_cast<char*>(smem + (size_t)(warp_base + src) * col_stride) + 16 * lane;
+#pragma unroll
+        for (int k = 0; k < kMaxPieces; ++k) {
+          if (lane + 32 * k < rec16) {
+            const bool live = pc_off[k] < (int)((m_src >> pc_shift[k]) & 0xff) * pc_per[k];
+            cp_async16(c_dst + 512 * k, r_src + 512 * k, live ? 16 : 0);
+          }
+        }
+      }
+    }
+    if (!busy_m) {
+      if (!staged_m) break;
+      continue;
+    }
+    T lsr = 0;  // idle lanes iterate their stale system: registers only, nothing is written
+    if (lmode == LAM_STACK) lsr = lam_round_stack(P, mx[BCP_PAIR_CART_POLE], mx[BCP_PAIR_GROUND_CART], Sy);
+    else lsr = lam_round_split<FRICTION>(P, fr, mx[BCP_PAIR_GROUND_POLE], mx[BCP_PAIR_GROUND_CART], Sy);
+    __syncwarp();
+    const bool busy = (busy_m >> lane) & 1u;
+    bool conv = false;
+    if (busy) {
+      it++;
+      conv = lsr <= res_thr || it >= max_it;
+    }
+    // a solve still running after handoff_it iterations leaves the pool: its system goes to the
+    // continuation buffer (STACK entries from the front, SPLIT from the back) and k_solve_tail
+    // finishes it in a densely packed, regime-pure warp
+    const bool hand = busy && !conv && handoff_it > 0 && it >= handoff_it;
+    const unsigned hm = __ballot_sync(FULL, hand);
+    if (hm) {
+      const unsigned hs = __ballot_sync(FULL, hand && lmode == LAM_STACK), hp = hm & ~hs;
+      int b0 = 0, b1 = 0;
+      if (lane == 0) {
+        if (hs) b0 = atomicAdd(&qc[2 * Q_WORDS + 0], __popc(hs));
+        if (hp) b1 = atomicAdd(&qc[2 * Q_WORDS + 1], __popc(hp));
+      }
+      b0 = __shfl_sync(FULL, b0, 0);
+      b1 = __shfl_sync(FULL, b1, 0);
+      if (hand) {
+        const int slot = lmode == LAM_STACK ? b0 + __popc(hs & lt) : N - 1 - (b1 + __popc(hp & lt));
+        lam_store(cont, N, slot, Sy);
+        contm[slot] = make_int4((int)((rec - recs) / rec_words), it, cnt[0] | (cnt[1] << 8) | (cnt[2] << 16), lmode);
+      }
+    }
+    const unsigned cm = __ballot_sync(FULL, conv) | hm;
+    if (cm) {
+      if (conv) {  // retire at once: bodies' deltas from the impulses and the rows still in the column
+        SolveRegs<T> R;
+        R.cart.invM = P.cart.inv_mass;
+        R.pole.invM = P.pole.inv_mass;
+        if (lmode == LAM_STACK) lam_finish_stack<true>(P, col + REC_ROWS, L, Sy, R);
+        else lam_finish_split<true, FRICTION>(P, col + REC_ROWS, L, Sy, R);
+        solve_end(rec, S, it, R);
+      }
+      busy_m &= ~cm;
+      const bool still = (busy_m >> lane) & 1u;
+#pragma unroll
+      for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, still ? cnt[m] : 0);
+    }
+  }
+}
+// The solves k_solve_lam handed off, one per lane, 32 consecutive continuation slots per warp (all
+// of one regime): no shared memory, no refill - every lane here needs tens of iterations, and an
+// iteration in impulse space is a short dependent chain.  Rows for the final body deltas come from
+// the env's solve record.
+template <typename T, bool FRICTION>
+__global__ void __launch_bounds__(kBlock, 2) k_solve_tail(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
+                                                           const int* __restrict__ qc, const T* __restrict__ cont,
+                                                           const int4* __restrict__ contm) {
+  const unsigned FULL = 0xffffffffu;
+  const int lane = threadIdx.x & 31;
+  const int N = P.num_envs;
+  const int n_stack = qc[2 * Q_WORDS + 0], n_split = qc[2 * Q_WORDS + 1];
+  const int c_stack = (n_stack + 31) >> 5, chunks = c_stack + ((n_split + 31) >> 5);
+  const SolveLayout L = solve_layout(P);
+  const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+  SolveScale<T> S;
+  {
+    SolveRegs<T> R0;
+    solve_consts(P, R0, S);
+  }
+  const T res_thr = P.residual_thr;
+  const int max_it = P.solver_iterations;
+  const int warps = gridDim.x * (blockDim.x >> 5);
+  for (int c = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); c < chunks; c += warps) {
+    const bool stack = c < c_stack;
+    const int k = stack ? c * 32 + lane : (c - c_stack) * 32 + lane;
+    bool busy = k < (stack ? n_stack : n_split);
+    const int slot = stack ? k : N - 1 - k;
+    LamSys<T> Sy;
+    int it = 0, meta = 0, env = 0;
+    if (busy) {
+      const int4 m = contm[slot];
+      env = m.x; it = m.y; meta = m.z;
+      lam_fetch(cont, N, slot, Sy);
+    }
+    int mx[3];
+#pragma unroll
+    for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? (meta >> (8 * m)) & 0xff : 0);
+    bool open = busy;
+    while (__any_sync(FULL, open)) {
+      if (open) {  // a lane that is done keeps its impulses untouched until the whole warp is
+        const T lsr = stack ? lam_round_stack(P, mx[BCP_PAIR_CART_POLE], mx[BCP_PAIR_GROUND_CART], Sy)
+                            : lam_round_split<FRICTION>(P, fr, mx[BCP_PAIR_GROUND_POLE], mx[BCP_PAIR_GROUND_CART], Sy);
+        it++;
+        if (lsr <= res_thr || it >= max_it) open = false;
+      }
+    }
+    if (busy) {  // all 32 at once: the record reads (one env per lane) overlap
+      T* rec = recs + (size_t)env * rec_words;
+      SolveRegs<T> R;
+      R.cart.invM = P.cart.inv_mass;
+      R.pole.invM = P.pole.inv_mass;
+      if (stack) lam_finish_stack<false>(P, rec + REC_ROWS, L, Sy, R);
+      else lam_finish_split<false, FRICTION>(P, rec + REC_ROWS, L, Sy, R);
+      solve_end(rec, S, it, R);
     }
   }
 }

@@ -24,3 +24,5 @@ print("regime (gc,cp,gp): count, long count, long frac")
 for k, n in sorted(tot.items(), key=lambda kv: -kv[1])[:25]:
     print(k, n, longs.get(k, 0), round(longs.get(k, 0) / n, 4))
 print("total long frac", sum(longs.values()) / sum(tot.values()))
+gen = {k: (n, longs.get(k, 0)) for k, n in tot.items() if k[1] > 0 and k[2] > 0}
+print("generic regimes (cp>0 and gp>0): envs", sum(v[0] for v in gen.values()), "of", sum(tot.values()), "long", sum(v[1] for v in gen.values()), "per call", sum(v[0] for v in gen.values()) / 12)
