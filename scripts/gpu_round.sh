@@ -18,9 +18,13 @@ timeout 900 python bench.py --envs 1048576 --steps 10 --no-cpu-baseline > $O/${T
 # and serialised, the kernels' SHARES are what is compared with the live numbers
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/${TAG}_launches.csv \
   python bench.py --steps 4 --warmup 3 --mix-calls 50 --no-cpu-baseline > $O/${TAG}_ncu_launches.log 2>&1
+timeout 600 python scripts/bench_replay.py > $O/${TAG}_replay_bench.json 2> $O/${TAG}_replay_bench.err
+BCP_REPLAY_GRAPH=0 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:k_rp_ -c 200 --csv --log-file $O/${TAG}_replay_launches.csv python scripts/bench_replay.py --warm 190 --steps 12 > $O/${TAG}_replay_ncu.log 2>&1
+BCP_LAMBDA=0 timeout 900 python bench.py --no-cpu-baseline > $O/${TAG}_bench_f32_rowspace.json 2> $O/${TAG}_bench_f32_rowspace.err
 export BCP_SPLIT=1
 python scripts/prof_split.py > $O/${TAG}_prof_plain.log 2>&1 && {
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_solve -s 4 -c 1 -f -o $O/${TAG}_k_solve python scripts/prof_split.py > $O/${TAG}_ncu_solve.log 2>&1
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_solve_lam -s 4 -c 1 -f -o $O/${TAG}_k_solve_lam python scripts/prof_split.py > $O/${TAG}_ncu_solve.log 2>&1
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_solve_tail -s 4 -c 1 -f -o $O/${TAG}_k_solve_tail python scripts/prof_split.py > $O/${TAG}_ncu_tail.log 2>&1
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_prep -s 7 -c 1 -f -o $O/${TAG}_k_prep python scripts/prof_split.py > $O/${TAG}_ncu_prep.log 2>&1
 }
 for f in $O/${TAG}_bench_*.json; do python - "$f" <<'PY'
