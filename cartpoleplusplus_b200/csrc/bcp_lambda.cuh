@@ -269,7 +269,7 @@ template <bool FRICTION, typename T> BCP_HD T lam_round_split(const Params<T>& P
       T dB = uB * S.invd[b], dA = uA * S.invd[a];
       BCP_LACC(cone_clip(S.lam[a], S.lam[b], dA, dB, uA, uB, DA, DB, mu * S.lam[c]));
 #pragma unroll
-      for (int k = 0; k < 12; ++k) S.res[k] -= S.A[tri(k, a)] * dA + S.A[tri(k, b)] * dB;
+      for (int k = 0; k < 12; ++k) { S.res[k] -= S.A[tri(k, a)] * dA; S.res[k] -= S.A[tri(k, b)] * dB; }
     }
   }
 #undef BCP_LACC

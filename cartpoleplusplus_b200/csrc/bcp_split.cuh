@@ -803,8 +803,9 @@ __global__ void __launch_bounds__(kBlock, 2) k_solve_tail(const __grid_constant_
     bool open = busy;
     while (__any_sync(FULL, open)) {
       if (open) {  // a lane that is done keeps its impulses untouched until the whole warp is
-        const T lsr = stack ? lam_round_stack(P, mx[BCP_PAIR_CART_POLE], mx[BCP_PAIR_GROUND_CART], Sy)
-                            : lam_round_split<FRICTION>(P, fr, mx[BCP_PAIR_GROUND_POLE], mx[BCP_PAIR_GROUND_CART], Sy);
+        // all four slots of every block, whatever the warp's counts (unused slots are zero rows):
+        // straight-line code, so the cart's rows schedule between the pole's
+        const T lsr = stack ? lam_round_stack(P, 4, 4, Sy) : lam_round_split<FRICTION>(P, fr, 4, 4, Sy);
         it++;
         if (lsr <= res_thr || it >= max_it) open = false;
       }
