@@ -318,7 +318,7 @@ def run_ours(args):
                    "auto_reset": "pipelined: a finished env runs its 130-substep reset R*S substeps per call; only env.steps "
                                  "actually taken are counted",
                    "phase_mix": f"stationary ({args.mix_calls} untimed random-agent calls before timing)",
-                   "l2": "flushed between steps (256 MiB memset, untimed)", "parallelism": f"env-sharded x{world}",
+                   "l2": "flushed between steps (256 MiB memset, untimed)", "parallelism": f"env-sharded x{world}", "pipeline": env.solver_kind,
                    "seed": args.seed},
         "live_fraction": live_all / (world * n * K),
         "slot_steps_per_s": world * n * K / (total_ms * 1e-3),

@@ -16,7 +16,7 @@ from typing import Optional
 
 from . import urdf as _urdf
 
-BCP_ABI_VERSION = 6
+BCP_ABI_VERSION = 7
 DTYPE_F32, DTYPE_F64 = 0, 1
 REASON_NAMES = {0: None, 1: "out of position bounds", 2: "out of orientation bounds", 3: "episode length",
                 4: "resetting", 5: "fresh"}

@@ -301,6 +301,12 @@ int bcp_bench_fma_peak(int device_ordinal, int use_f64, int iters, double* tflop
 
 int64_t bcp_launch_count(const bcp_env* h) { return h ? h->launches : 0; }
 
+int bcp_solver_kind(const bcp_env* env) {
+  if (!env) return fail("bcp_solver_kind: null handle");
+  if (env->f64() || !env->use_split || !env->split.recs) return BCP_SOLVER_ONE_LAUNCH;
+  return (env->split.cont && bcp::split_uses_lambda(env->p32)) ? BCP_SOLVER_SPLIT_IMPULSE : BCP_SOLVER_SPLIT_ROW;
+}
+
 int bcp_profile_begin(bcp_env* h) {
   if (!h) return fail("bcp_profile_begin: null handle");
   for (cudaEvent_t e : h->prof_events) cudaEventDestroy(e);

@@ -10,6 +10,16 @@ size_t split_counter_words(const Params<float>& P) { return (size_t)(P.R * P.S) 
 size_t split_cont_words(const Params<float>& P) { return (size_t)LAM_WORDS * (size_t)P.num_envs; }
 size_t split_bins_words(const Params<float>& P) { return (size_t)N_BINS * (size_t)P.num_envs; }
 
+bool split_uses_lambda(const Params<float>& P) {
+  static int lam_env = -2;
+  if (lam_env == -2) {
+    const char* le = getenv("BCP_LAMBDA");
+    lam_env = le ? atoi(le) : -1;
+  }
+  const bool wanted = lam_env < 0 ? P.num_envs < 131072 : lam_env != 0;
+  return wanted && lam_config_ok(P);
+}
+
 template <bool FRICTION>
 static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, SplitBuffers& b, const SplitIO& io,
                                    const Stats& st, cudaStream_t s, int* launches, std::vector<cudaEvent_t>* prof) {
@@ -47,13 +57,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   // (measured on B200: +6..7 % env-steps/s at 32 768 and 65 536 envs, equal at 131 072); beyond
   // that the phase is issue-bound and building the matrices costs more than it saves (-3 % at
   // 262 144, -8 % at 1 M).  BCP_LAMBDA=1 / 0 forces it on / off.
-  static int lam_env = -2;
-  if (lam_env == -2) {
-    const char* le = getenv("BCP_LAMBDA");
-    lam_env = le ? atoi(le) : -1;
-  }
-  const bool lam_wanted = lam_env < 0 ? N < 131072 : lam_env != 0;
-  const int use_lam = (lam_wanted && lam_config_ok(P) && b.cont) ? 1 : 0;
+  const int use_lam = (split_uses_lambda(P) && b.cont) ? 1 : 0;
   static int handoff = -1;
   if (handoff < 0) {
     const char* he = getenv("BCP_HANDOFF");

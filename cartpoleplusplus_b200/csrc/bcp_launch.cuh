@@ -44,6 +44,7 @@ struct SplitBuffers {
   cudaEvent_t ev_prep, ev_gen;
 };
 size_t split_cont_words(const Params<float>& P);
+bool split_uses_lambda(const Params<float>& P);  // impulse-space solve phase for this configuration / batch size?
 size_t split_bins_words(const Params<float>& P);
 size_t split_record_words(const Params<float>& P);
 size_t split_counter_words(const Params<float>& P);

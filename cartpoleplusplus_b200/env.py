@@ -231,6 +231,11 @@ class BatchedBulletCartpole:
         return {"ms_prep": out[0], "ms_solve": out[1], "n_prep": int(out[2]), "n_solve": int(out[3])}
 
     @property
+    def solver_kind(self) -> str:
+        """which pipeline step() runs: 'one-launch', 'split/row-space' or 'split/impulse-space'"""
+        return ("one-launch", "split/row-space", "split/impulse-space")[int(self._lib.bcp_solver_kind(self._h))]
+
+    @property
     def launch_count(self) -> int:
         return int(self._lib.bcp_launch_count(self._h))
 

@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define BCP_ABI_VERSION 6
+#define BCP_ABI_VERSION 7
 
 /* ---- dtype of the physics arithmetic ------------------------------------ */
 #define BCP_DTYPE_F32 0 /* fast mode                                          */
@@ -224,6 +224,14 @@ int bcp_substep(bcp_env* env, void* stream);
  * (2 flops per FMA).  Gives the FP32 / FP64 CUDA-core pipe peak the roofline of this
  * compute-bound path is quoted against (MEASURED_PEAKS.json has no such entry). */
 int bcp_bench_fma_peak(int device_ordinal, int use_f64, int iters, double* tflops_out);
+
+/* Which pipeline bcp_step runs on this handle (reporting only; results agree to fp32 rounding):
+ * the one-launch kernel (fp64, small batches), the split pipeline with the row-space solver, or
+ * the split pipeline with the impulse-space solve phase.              */
+#define BCP_SOLVER_ONE_LAUNCH 0
+#define BCP_SOLVER_SPLIT_ROW 1
+#define BCP_SOLVER_SPLIT_IMPULSE 2
+int bcp_solver_kind(const bcp_env* env);
 
 /* number of kernel launches this handle has enqueued (bench's gpu_launches) */
 int64_t bcp_launch_count(const bcp_env* env);
