@@ -48,8 +48,18 @@ struct bcp_env {
   int* list = nullptr;   // compacted env indices for masked resets
   int* count = nullptr;
   double* staging = nullptr;  // canonical records for get/set_state
-  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
+  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
   int use_split = 0;
+  // bcp_step_host: device-side actions / outputs / packed observation slabs, the copy stream
+  struct HostStep {
+    void* d_act = nullptr;
+    unsigned char* d_out = nullptr;  // obs f32[N][R][14] | reward f32[N] | done u8[N] | reason u8[N]
+    float* d_slab = nullptr;         // [R][N][14]
+    cudaStream_t copy = nullptr;
+    cudaEvent_t ev_ready = nullptr, ev_copied = nullptr;
+    float* h_obs = nullptr;          // this call's host slabs
+    bool fired = false;
+  } hs;
   bool profiling = false;
   std::vector<cudaEvent_t> prof_events;  // bracketing every kernel of bcp_step while profiling
   std::vector<int> prof_calls;           // events per bcp_step call
@@ -161,6 +171,10 @@ int bcp_destroy(bcp_env* h) {
   DeviceGuard g(h->cfg.device_ordinal);
   cudaFree(h->fdata); cudaFree(h->idata); cudaFree(h->hist); cudaFree(h->header);
   cudaFree(h->reward_sum); cudaFree(h->list); cudaFree(h->count); cudaFree(h->staging);
+  if (h->hs.d_out) {
+    cudaFree(h->hs.d_act); cudaFree(h->hs.d_out); cudaFree(h->hs.d_slab);
+    cudaStreamDestroy(h->hs.copy); cudaEventDestroy(h->hs.ev_ready); cudaEventDestroy(h->hs.ev_copied);
+  }
   if (h->split.side) { cudaStreamDestroy(h->split.side); cudaEventDestroy(h->split.ev_prep); cudaEventDestroy(h->split.ev_gen); }
   cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc); cudaFree(h->split.cont); cudaFree(h->split.contm);
   for (int k = 0; k < 2; ++k) { cudaFree(h->split.bins[k]); cudaFree(h->split.cnts[k]); }
@@ -205,6 +219,108 @@ int bcp_step(bcp_env* h, const void* actions, float* obs_out, float* reward_out,
   else CK(bcp::Launch<float>::step(h->p32, h->fdata, h->idata, actions, obs_out, reward_out, done_out, reason_out, h->stats(), s));
   if (h->profiling) { cudaEventRecord(e1, s); h->prof_events.push_back(e0); h->prof_events.push_back(e1); h->prof_calls.push_back(2); }
   h->launches++;
+  return 0;
+}
+
+// ---- bcp_step_host: env.step with HOST buffers, copies overlapped with the kernels ----
+namespace {
+__global__ void k_pack_slab(const float* __restrict__ obs, float* __restrict__ slab, int n, int R, int r) {
+  // obs f32[n][R][14] -> slab f32[n][14] (repeat r), one thread per float2
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * 7) return;
+  const int e = i / 7, w = i - e * 7;
+  reinterpret_cast<float2*>(slab)[i] = reinterpret_cast<const float2*>(obs + ((size_t)e * R + r) * 14)[w];
+}
+void pack_and_copy(bcp_env* h, int r, cudaStream_t s) {
+  const int n = h->cfg.num_envs, R = h->cfg.action_repeats;
+  float* slab = h->hs.d_slab + (size_t)r * n * 14;
+  k_pack_slab<<<(n * 7 + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float*>(h->hs.d_out), slab, n, R, r);
+  cudaMemcpyAsync(h->hs.h_obs + (size_t)r * n * 14, slab, (size_t)n * 14 * sizeof(float), cudaMemcpyDeviceToHost, s);
+  h->launches++;
+}
+// after the k-th k_prep of a split call: repeat r = k / S - 1 is complete when k is a multiple of S
+void host_step_hook(void* ctx, int k, cudaStream_t s) {
+  bcp_env* h = static_cast<bcp_env*>(ctx);
+  const int R = h->cfg.action_repeats, S = h->cfg.steps_per_repeat;
+  if (k <= 0 || k >= R * S || k % S) return;  // the last repeat leaves with the call's other outputs
+  cudaEventRecord(h->hs.ev_ready, s);
+  cudaStreamWaitEvent(h->hs.copy, h->hs.ev_ready, 0);
+  pack_and_copy(h, k / S - 1, h->hs.copy);
+  cudaEventRecord(h->hs.ev_copied, h->hs.copy);
+  h->hs.fired = true;
+}
+}  // namespace
+
+int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_reward, uint8_t* h_done, uint8_t* h_reason,
+                  void* stream) {
+  if (!h) return fail("bcp_step_host: null handle");
+  if (!h_actions || !h_obs_rm || !h_reward || !h_done || !h_reason) return fail("bcp_step_host: null argument");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  const size_t n = (size_t)h->cfg.num_envs, R = (size_t)h->cfg.action_repeats;
+  const size_t ob = n * R * 14 * sizeof(float), rb = n * sizeof(float);
+  const size_t ab = n * (h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float));
+  if (!h->hs.d_out) {
+    CK(cudaMalloc(&h->hs.d_act, ab));
+    CK(cudaMalloc((void**)&h->hs.d_out, ob + rb + 2 * n));
+    CK(cudaMalloc((void**)&h->hs.d_slab, ob));
+    {
+      int lo = 0, hi = 0;
+      cudaDeviceGetStreamPriorityRange(&lo, &hi);
+      CK(cudaStreamCreateWithPriority(&h->hs.copy, cudaStreamNonBlocking, hi));  // its pack kernel goes first when blocks retire
+    }
+    CK(cudaEventCreateWithFlags(&h->hs.ev_ready, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->hs.ev_copied, cudaEventDisableTiming));
+  }
+  float* d_obs = reinterpret_cast<float*>(h->hs.d_out);
+  float* d_rew = reinterpret_cast<float*>(h->hs.d_out + ob);
+  uint8_t* d_done = h->hs.d_out + ob + rb;
+  uint8_t* d_reason = d_done + n;
+  CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, s));
+  h->hs.h_obs = h_obs_rm;
+  h->hs.fired = false;
+  const bool split = !h->f64() && h->use_split;
+  if (split) { h->split.after_prep = host_step_hook; h->split.hook_ctx = h; }
+  const int rc = bcp_step(h, h->hs.d_act, d_obs, d_rew, d_done, d_reason, stream);
+  h->split.after_prep = nullptr;
+  if (rc) return rc;
+  // the repeats that did not leave during the call (all of them on the one-launch pipeline)
+  for (int r = h->hs.fired ? (int)R - 1 : 0; r < (int)R; ++r) pack_and_copy(h, r, s);
+  if (reinterpret_cast<uint8_t*>(h_reward) + rb == h_done && h_done + n == h_reason) {
+    CK(cudaMemcpyAsync(h_reward, d_rew, rb + 2 * n, cudaMemcpyDeviceToHost, s));  // one transfer when the caller's buffers are adjacent
+  } else {
+    CK(cudaMemcpyAsync(h_reward, d_rew, rb, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h_done, d_done, n, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h_reason, d_reason, n, cudaMemcpyDeviceToHost, s));
+  }
+  if (h->hs.fired) CK(cudaStreamWaitEvent(s, h->hs.ev_copied, 0));  // a sync on `stream` covers the early slabs too
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int bcp_step_host_finish(bcp_env* h, float* h_obs_rm, const uint8_t* h_reason, void* stream) {
+  if (!h || !h_obs_rm || !h_reason) return fail("bcp_step_host_finish: null argument");
+  DeviceGuard g(h->cfg.device_ordinal);
+  CK(cudaStreamSynchronize((cudaStream_t)stream));
+  // An env whose pipelined reset ended in this call (FRESH) gets its reset observation in every
+  // repeat slot when the call closes (bullet_cartpole.py:338-339) - after the early slabs left.
+  const size_t n = (size_t)h->cfg.num_envs;
+  const int R = h->cfg.action_repeats;
+  if (R > 1 && h->cfg.auto_reset == BCP_AUTO_RESET_PIPELINED) {
+    const float* last = h_obs_rm + (size_t)(R - 1) * n * 14;
+    auto patch = [&](size_t e) {
+      for (int r = 0; r < R - 1; ++r) memcpy(h_obs_rm + ((size_t)r * n + e) * 14, last + e * 14, 14 * sizeof(float));
+    };
+    size_t e = 0;
+    for (; e + 8 <= n; e += 8) {  // eight reason bytes at a time: any equal to BCP_REASON_FRESH?
+      uint64_t w;
+      memcpy(&w, h_reason + e, 8);
+      w ^= 0x0505050505050505ull;
+      if ((w - 0x0101010101010101ull) & ~w & 0x8080808080808080ull)
+        for (size_t k = e; k < e + 8; ++k) if (h_reason[k] == BCP_REASON_FRESH) patch(k);
+    }
+    for (; e < n; ++e) if (h_reason[e] == BCP_REASON_FRESH) patch(e);
+  }
   return 0;
 }
 

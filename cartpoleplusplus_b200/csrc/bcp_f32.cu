@@ -118,6 +118,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
     int* qc = b.qc + (size_t)(k < RS ? k : 0) * 3 * Q_WORDS;
     k_prep<float, FRICTION><<<prep_grid, prep_block, prep_smem, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set, use_lam);
     if (launches) ++*launches;
+    if (b.after_prep) b.after_prep(b.hook_ctx, k, s);
     mark();
     if (k < RS) {
       if (use_lam) {

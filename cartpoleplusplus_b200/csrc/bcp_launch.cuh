@@ -42,6 +42,10 @@ struct SplitBuffers {
   // the generic queue's k_solve runs beside the impulse-space kernels on a high-priority side stream
   cudaStream_t side;
   cudaEvent_t ev_prep, ev_gen;
+  // optional: called right after the k-th k_prep of a call has been enqueued on `s` (bcp_step_host
+  // starts the device->host copy of an observation slab as soon as its repeat is complete)
+  void (*after_prep)(void* ctx, int k, cudaStream_t s);
+  void* hook_ctx;
 };
 size_t split_cont_words(const Params<float>& P);
 bool split_uses_lambda(const Params<float>& P);  // impulse-space solve phase for this configuration / batch size?

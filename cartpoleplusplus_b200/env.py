@@ -133,26 +133,46 @@ class BatchedBulletCartpole:
 
     # ---- host-buffer call: what a CPU-side agent loop uses (pinned buffers, one sync) ----
     def step_host(self, actions_host: torch.Tensor, auto_reset: bool = False):
-        """env.step with HOST tensors: H2D of the actions, the step kernel, (optionally) the
-        reset of finished envs, D2H of obs/reward/done into pinned buffers, one stream sync.
-        Returns pinned CPU tensors (overwritten by the next call)."""
+        """env.step with HOST tensors through bcp_step_host: H2D of the actions, the step kernels, D2H of
+        obs/reward/done into pinned buffers - the observation slab of a repeat leaves as soon as that
+        repeat is complete, beside the remaining substeps - one stream sync.  Returns CPU tensors
+        (views of pinned buffers, overwritten by the next call): obs (B,R,2,7) as a permuted view of
+        the repeat-major buffer the copies fill, reward (B,), done (B,) uint8.
+        auto_reset=True (reset(mask=done) after the step, so that the next observation of a finished
+        env is its reset observation) takes the plain path: step, one D2H, reset."""
+        n, R = self.num_envs, self.repeats
         if not hasattr(self, "_h_out"):
-            n, ob, rb = self.num_envs, self.obs.numel() * 4, self.num_envs * 4
+            ob, rb = self.obs.numel() * 4, n * 4
             self._h_out = torch.empty(self._out.numel(), dtype=torch.uint8).pin_memory()
             self._h_obs = self._h_out[:ob].view(torch.float32).view(self.obs.shape)
+            self._h_obs_rm = self._h_out[:ob].view(torch.float32).view(R, n, 2, 7)  # the same bytes, repeat-major
             self._h_reward = self._h_out[ob:ob + rb].view(torch.float32)
             self._h_done = self._h_out[ob + rb:ob + rb + n]
             self._h_reason = self._h_out[ob + rb + n:]
             adt = torch.int32 if self.discrete_actions else torch.float32
-            ashape = (self.num_envs,) if self.discrete_actions else (self.num_envs, 2)
+            ashape = (n,) if self.discrete_actions else (n, 2)
             self._d_act = torch.empty(ashape, dtype=adt, device=self.device)
-        self._d_act.copy_(actions_host.reshape(self._d_act.shape), non_blocking=True)
-        self.step(self._d_act, copy=False)
-        self._h_out.copy_(self._out, non_blocking=True)  # obs, reward, done, reason in one transfer
-        if auto_reset:  # the next observation of a finished env is its reset observation
+            self._h_act = torch.empty(ashape, dtype=adt).pin_memory()
+        if auto_reset:
+            self._d_act.copy_(actions_host.reshape(self._d_act.shape), non_blocking=True)
+            self.step(self._d_act, copy=False)
+            self._h_out.copy_(self._out, non_blocking=True)  # obs, reward, done, reason in one transfer
             self.reset(mask=self.done, copy=False)
-        torch.cuda.current_stream(self.device).synchronize()
-        return self._h_obs, self._h_reward, self._h_done
+            torch.cuda.current_stream(self.device).synchronize()
+            return self._h_obs, self._h_reward, self._h_done
+        if not self._was_reset:
+            raise _lib.BcpError("step() before reset()")
+        a = actions_host
+        if not (type(a) is torch.Tensor and a.dtype == self._h_act.dtype and a.is_pinned() and a.is_contiguous()
+                and a.numel() == self._h_act.numel()):
+            self._h_act.copy_(torch.as_tensor(actions_host).reshape(self._h_act.shape))
+            a = self._h_act
+        vp = ctypes.c_void_p
+        st = self._stream()
+        _lib.check(self._lib.bcp_step_host(self._h, vp(a.data_ptr()), vp(self._h_obs_rm.data_ptr()), vp(self._h_reward.data_ptr()),
+                                           vp(self._h_done.data_ptr()), vp(self._h_reason.data_ptr()), st), self._lib)
+        _lib.check(self._lib.bcp_step_host_finish(self._h, vp(self._h_obs_rm.data_ptr()), vp(self._h_reason.data_ptr()), st), self._lib)
+        return self._h_obs_rm.permute(1, 0, 2, 3), self._h_reward, self._h_done
 
     @property
     def h2d_bytes_per_step(self) -> int:

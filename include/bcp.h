@@ -215,6 +215,19 @@ int bcp_stats_clear(bcp_env* env, void* stream);
 int bcp_get_state(bcp_env* env, double* host_buf, size_t n_doubles, void* stream);
 int bcp_set_state(bcp_env* env, const double* host_buf, size_t n_doubles, void* stream);
 
+/* bcp_step for a HOST-side agent loop: actions in from, and the four outputs out to, host buffers
+ * (pinned memory for the copies to overlap), all enqueued on `stream`.  The observation leaves
+ * repeat by repeat - the slab of repeat r is copied on a second stream as soon as the kernel that
+ * completes it is done, beside the remaining substeps - so it arrives REPEAT-MAJOR:
+ *   h_obs_rm f32[R][num_envs][2][7]   (h_obs_rm[r][e] == obs_out[e][r] of bcp_step)
+ *   h_actions i32[num_envs] | f32[num_envs][2];  h_reward f32[num_envs], h_done / h_reason u8[num_envs]
+ * bcp_step_host_finish synchronises `stream` and completes the buffers on the host (the envs whose
+ * pipelined reset ended in the call receive their reset observation in every repeat slot only when
+ * the call closes, :338-339); call it before reading.                                            */
+int bcp_step_host(bcp_env* env, const void* h_actions, float* h_obs_rm, float* h_reward, uint8_t* h_done,
+                  uint8_t* h_reason, void* stream);
+int bcp_step_host_finish(bcp_env* env, float* h_obs_rm, const uint8_t* h_reason, void* stream);
+
 /* One bare p.stepSimulation() for every env (no force application, no
  * bookkeeping) - bullet_cartpole.py:199 alone; used by single-substep parity. */
 int bcp_substep(bcp_env* env, void* stream);

@@ -61,3 +61,33 @@ for _ in range(K):
 t1 = time.perf_counter()
 torch.cuda.synchronize()
 print("enqueue per step", round((t1 - t0) / K * 1e3, 4), "ms")
+
+import time as _t
+torch.cuda.synchronize()
+t0 = _t.perf_counter()
+for _ in range(50):
+    o, r, d = env.step_host(ha)
+    s_ = int(r.sum().item())
+t1 = _t.perf_counter()
+print("step_host (bcp_step_host) wall per step incl. reward read:", round((t1 - t0) / 50 * 1e3, 4), "ms")
+
+import ctypes
+vp = ctypes.c_void_p
+lib = env._lib
+st = env._stream()
+ta = tb = 0.0
+e0, e1 = ev(), ev()
+gpu = 0.0
+for _ in range(50):
+    t0 = _t.perf_counter()
+    e0.record()
+    lib.bcp_step_host(env._h, vp(ha.data_ptr()), vp(env._h_obs_rm.data_ptr()), vp(env._h_reward.data_ptr()), vp(env._h_done.data_ptr()), vp(env._h_reason.data_ptr()), st)
+    e1.record()
+    t1 = _t.perf_counter()
+    torch.cuda.current_stream().synchronize()
+    t2 = _t.perf_counter()
+    lib.bcp_step_host_finish(env._h, vp(env._h_obs_rm.data_ptr()), vp(env._h_reason.data_ptr()), st)
+    t3 = _t.perf_counter()
+    ta += t1 - t0; tb += t2 - t1; gpu += e0.elapsed_time(e1)
+    if _ == 0: first = (t3 - t2)
+print("bcp_step_host enqueue", round(ta / 50 * 1e3, 4), "wait", round(tb / 50 * 1e3, 4), "gpu e0->e1", round(gpu / 50, 4), "finish (patch) first", round(first * 1e3, 4), "ms")
