@@ -124,35 +124,72 @@ def cpu_baseline(args, budget_s=12.0):
 
 
 class ClockSampler(threading.Thread):
-    """nvidia-smi clocks / throttle reasons during the timed region."""
+    """SM clock, power and throttle reasons sampled DURING the timed regions.
+
+    NVML in-process (about a millisecond per sample, so that even a 15 ms timed region gets several);
+    the nvidia-smi query of the profiling recipe is the fallback when NVML cannot be loaded."""
 
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
 
-    def __init__(self, index):
+    def __init__(self, index, uuid=None):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
+        self.nvml = self.handle = None
+        self.source = "nvidia-smi"
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            try:
+                self.handle = pynvml.nvmlDeviceGetHandleByUUID(uuid.encode()) if uuid else None
+            except Exception:
+                self.handle = None
+            if self.handle is None:
+                self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.nvml, self.source = pynvml, "nvml"
+        except Exception:
+            self.nvml = None
+
+    def sample(self):
+        """-> [sm_mhz, sm_max_mhz, power_w, hw_slowdown, hw_thermal, sw_thermal, sw_power_cap] (flags 0/1)"""
+        if self.nvml is not None:
+            n, h = self.nvml, self.handle
+            sm = n.nvmlDeviceGetClockInfo(h, n.NVML_CLOCK_SM)
+            mx = n.nvmlDeviceGetMaxClockInfo(h, n.NVML_CLOCK_SM)
+            try:
+                pw = n.nvmlDeviceGetPowerUsage(h) / 1000.0
+            except Exception:
+                pw = 0.0
+            r = n.nvmlDeviceGetCurrentClocksEventReasons(h)
+            bits = [n.nvmlClocksEventReasonHwSlowdown, n.nvmlClocksEventReasonHwThermalSlowdown,
+                    n.nvmlClocksEventReasonSwThermalSlowdown, n.nvmlClocksEventReasonSwPowerCap]
+            return [float(sm), float(mx), pw] + [1 if r & b else 0 for b in bits]
+        out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                              "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
+        c = [x.strip() for x in out.strip().split(",")]
+        return [float(c[0]), float(c[1]), float(c[2])] + [1 if x.lower().startswith("active") else 0 for x in c[3:7]]
 
     def run(self):
         while not self.stop_flag:
             try:
-                out = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                                      "-i", str(self.index)], capture_output=True, text=True, timeout=5).stdout
-                self.rows.append([c.strip() for c in out.strip().split(",")])
+                self.rows.append(self.sample())
             except Exception:
                 pass
-            time.sleep(0.05)
+            time.sleep(0.002 if self.nvml is not None else 0.05)
 
     def summary(self):
+        self.stop_flag = True
+        if self.is_alive():
+            self.join(timeout=6)
         rows = [r for r in self.rows if len(r) >= 7]
         if not rows:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"]}
-        sm = sorted(float(r[0]) for r in rows)
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
-        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": float(rows[0][1]), "reasons": reasons,
-                "power_w_max": max(float(r[2]) for r in rows), "samples": len(rows)}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["unavailable"], "source": self.source}
+        sm = sorted(r[0] for r in rows)
+        reasons = [n for i, n in enumerate(self.NAMES) if any(r[3 + i] for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": rows[0][1], "reasons": reasons,
+                "power_w_max": max(r[2] for r in rows), "samples": len(rows), "source": self.source}
 
 
 # ---------------------------------------------------------------------------------------
@@ -200,7 +237,12 @@ def run_ours(args):
     torch.cuda.synchronize()
     env.clear_stats()
     launches0 = env.launch_count
-    sampler = ClockSampler(local)
+    try:
+        uuid = str(torch.cuda.get_device_properties(local).uuid)
+        uuid = uuid if uuid.startswith("GPU-") else "GPU-" + uuid
+    except Exception:
+        uuid = None
+    sampler = ClockSampler(local, uuid)  # runs through both timed regions (device-timed steps, then e2e)
     sampler.start()
     env.profile_begin()
     if world > 1:
@@ -212,7 +254,6 @@ def run_ours(args):
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-    sampler.stop_flag = True
     prof = env.profile_end()
     total_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
     launches = env.launch_count - launches0
@@ -223,7 +264,7 @@ def run_ours(args):
     host_actions = [torch.empty((n, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
     for h in host_actions:
         h.uniform_(-1, 1)
-    Ke = max(3, min(K, 20))
+    Ke = max(3, K)
     for t in range(2):
         env.step_host(host_actions[t % 2])
     if world > 1:
@@ -236,6 +277,7 @@ def run_ours(args):
         e2e_live += int(rew.sum().item())
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
+    sampler.stop_flag = True
 
     # ---- max over ranks of the times, sums of the counts; the one collective: statistics allreduce ----
     tt = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
@@ -393,8 +435,8 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=40)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=10)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--envs", type=int, default=65536, help="envs per GPU")
     ap.add_argument("--dtype", default="fp32", choices=["fp32", "fp64"])

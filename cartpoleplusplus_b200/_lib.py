@@ -14,7 +14,9 @@ EXPORTS = ["bcp_abi_version", "bcp_config_size", "bcp_last_error", "bcp_create",
            "bcp_substep", "bcp_launch_count", "bcp_bench_fma_peak", "bcp_profile_begin", "bcp_profile_end", "bcp_last_solve_info", "bcp_solver_kind", "bcp_step_host", "bcp_step_host_finish",
            # include/bcp_replay.h
            "bcp_replay_config_size", "bcp_replay_create", "bcp_replay_destroy", "bcp_replay_begin", "bcp_replay_observe",
-           "bcp_replay_add_episode", "bcp_replay_batch", "bcp_replay_info", "bcp_replay_export", "bcp_replay_launch_count"]
+           "bcp_replay_add_episode", "bcp_replay_batch", "bcp_replay_info", "bcp_replay_export", "bcp_replay_launch_count",
+           # include/bcp_lqr.h
+           "bcp_lqr_args_size", "bcp_lqr_control"]
 
 REPLAY_ABI_VERSION = 1
 REPLAY_INFO_WORDS = 10
@@ -26,6 +28,14 @@ class BcpReplayConfig(ctypes.Structure):
     _fields_ = [("abi_version", ctypes.c_int32), ("device_ordinal", ctypes.c_int32), ("buffer_size", ctypes.c_int64),
                 ("state_buffer_size", ctypes.c_int64), ("state_words", ctypes.c_int32), ("action_dim", ctypes.c_int32),
                 ("num_envs", ctypes.c_int32), ("max_episode_len", ctypes.c_int32)]
+
+
+class BcpLqrArgs(ctypes.Structure):
+    """mirror of bcp_lqr_args (include/bcp_lqr.h)"""
+    _fields_ = [("gains", ctypes.c_void_p), ("gains_per_env", ctypes.c_int32), ("zero_point", ctypes.c_void_p),
+                ("x0", ctypes.c_void_p), ("disturbance", ctypes.c_void_p), ("disturbance_per_env", ctypes.c_int32),
+                ("position_threshold", ctypes.c_float), ("angle_threshold", ctypes.c_float),
+                ("state_out", ctypes.c_void_p), ("action_out", ctypes.c_void_p), ("done_out", ctypes.c_void_p)]
 
 
 class BcpError(RuntimeError):
@@ -79,12 +89,16 @@ def load(build_if_missing: bool = False):
     lib.bcp_replay_export.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp]
     lib.bcp_replay_launch_count.argtypes = [vp]
     lib.bcp_replay_launch_count.restype = i64
+    lib.bcp_lqr_args_size.restype = ctypes.c_size_t
+    lib.bcp_lqr_control.argtypes = [vp, ctypes.POINTER(BcpLqrArgs), vp]
     if lib.bcp_abi_version() != C.BCP_ABI_VERSION:
         raise BcpError(f"libbcp.so ABI {lib.bcp_abi_version()} != python mirror {C.BCP_ABI_VERSION}: rebuild")
     if lib.bcp_config_size() != ctypes.sizeof(C.BcpConfig):
         raise BcpError("sizeof(bcp_config) differs between libbcp.so and the ctypes mirror: rebuild")
     if lib.bcp_replay_config_size() != ctypes.sizeof(BcpReplayConfig):
         raise BcpError("sizeof(bcp_replay_config) differs between libbcp.so and the ctypes mirror: rebuild")
+    if lib.bcp_lqr_args_size() != ctypes.sizeof(BcpLqrArgs):
+        raise BcpError("sizeof(bcp_lqr_args) differs between libbcp.so and the ctypes mirror: rebuild")
     _LIB = lib
     return lib
 

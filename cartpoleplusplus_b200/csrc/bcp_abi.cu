@@ -9,6 +9,7 @@
 #include <vector>
 
 #include "../../include/bcp.h"
+#include "../../include/bcp_lqr.h"
 #include "bcp_launch.cuh"
 #include "bcp_state.cuh"
 
@@ -468,6 +469,89 @@ int bcp_last_solve_info(bcp_env* h, int32_t* host_out, size_t n_ints, void* stre
   CK(cudaMemcpy2DAsync(host_out, 4 * sizeof(int32_t), h->split.recs, pitch, 4 * sizeof(int32_t), (size_t)h->cfg.num_envs,
                        cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- the fork's 8-state observation and LQR feedback (include/bcp_lqr.h) ----
+namespace {
+
+// pybullet's getEulerFromQuaternion (q = x,y,z,w): roll and pitch only, with its gimbal-lock branches
+template <typename T> __device__ void roll_pitch(const T* q, T& roll, T& pitch) {
+  const T sqx = q[0] * q[0], sqy = q[1] * q[1], sqz = q[2] * q[2], squ = q[3] * q[3];
+  const T sarg = T(-2) * (q[0] * q[2] - q[3] * q[1]);
+  const T half_pi = T(1.5707963267948966);
+  if (sarg <= T(-0.99999)) { roll = 0; pitch = -half_pi; }
+  else if (sarg >= T(0.99999)) { roll = 0; pitch = half_pi; }
+  else { roll = atan2(T(2) * (q[1] * q[2] + q[3] * q[0]), squ - sqx - sqy + sqz); pitch = asin(sarg); }
+}
+
+template <typename T> __global__ void k_lqr(int N, const T* __restrict__ f, bcp_lqr_args a) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= N) return;
+  const T* b = f + (size_t)e * bcp::NF + BCP_S_POLE;  // x[3] q[4] v[3] w[3]
+  T q[4] = {b[3], b[4], b[5], b[6]}, roll, pitch;
+  roll_pitch(q, roll, pitch);
+  float st[BCP_LQR_STATE];
+  st[0] = (float)(b[0] - (a.x0 ? (T)a.x0[e] : T(0)));
+  st[1] = (float)b[7];
+  st[2] = (float)b[1];
+  st[3] = (float)b[8];
+  st[4] = (float)roll;
+  st[5] = (float)b[10];
+  st[6] = (float)pitch;
+  st[7] = (float)b[11];
+  if (a.state_out) {
+    float4* o = reinterpret_cast<float4*>(a.state_out + (size_t)e * BCP_LQR_STATE);
+    o[0] = make_float4(st[0], st[1], st[2], st[3]);
+    o[1] = make_float4(st[4], st[5], st[6], st[7]);
+  }
+  if (a.done_out) {
+    uint8_t d = BCP_LQR_RUNNING;
+    if (fabsf(st[0]) > a.position_threshold || fabsf(st[2]) > a.position_threshold) d = BCP_LQR_POSITION;
+    else if (fabsf(st[4]) > a.angle_threshold || fabsf(st[6]) > a.angle_threshold) d = BCP_LQR_ANGLE;
+    a.done_out[e] = d;
+  }
+  if (a.action_out) {
+    float u[BCP_LQR_ACTIONS] = {0.f, 0.f};
+    if (a.gains) {
+      const float* K = a.gains + (a.gains_per_env ? (size_t)e * BCP_LQR_ACTIONS * BCP_LQR_STATE : 0);
+      for (int i = 0; i < BCP_LQR_ACTIONS; ++i) {
+        // numpy's dot of float64 operands in the fork; here the f32 state against f32 gains, summed in order
+        float acc = 0.f;
+        for (int j = 0; j < BCP_LQR_STATE; ++j)  // no FMA contraction: the oracle's numpy float32 sum, bit for bit
+          acc = __fadd_rn(acc, __fmul_rn(K[i * BCP_LQR_STATE + j], st[j] - (a.zero_point ? a.zero_point[j] : 0.f)));
+        u[i] = -acc;
+      }
+    }
+    if (a.disturbance) {
+      const float* d = a.disturbance + (a.disturbance_per_env ? (size_t)e * BCP_LQR_ACTIONS : 0);
+      u[0] += d[0];
+      u[1] += d[1];
+    }
+    *reinterpret_cast<float2*>(a.action_out + (size_t)e * BCP_LQR_ACTIONS) = make_float2(u[0], u[1]);
+  }
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t bcp_lqr_args_size(void) { return sizeof(bcp_lqr_args); }
+
+int bcp_lqr_control(bcp_env* h, const bcp_lqr_args* args, void* stream) {
+  if (!h || !args) return fail("bcp_lqr_control: null argument");
+  if (!args->state_out && !args->action_out && !args->done_out) return fail("bcp_lqr_control: no output requested");
+  if (args->done_out && !(args->position_threshold > 0.f && args->angle_threshold > 0.f))
+    return fail("bcp_lqr_control: thresholds must be positive");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int N = h->cfg.num_envs, block = 128, grid = (N + block - 1) / block;
+  if (h->f64()) k_lqr<double><<<grid, block, 0, s>>>(N, (const double*)h->fdata, *args);
+  else k_lqr<float><<<grid, block, 0, s>>>(N, (const float*)h->fdata, *args);
+  CK(cudaGetLastError());
+  ++h->launches;
   return 0;
 }
 
