@@ -42,6 +42,12 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   vo.cnt = b.cur < 0 ? nullptr : b.cnts[b.cur];
   vo.next_bins = b.bins[nxt];
   vo.next_cnt = b.cnts[nxt];
+  static int visit_rev = -1;
+  if (visit_rev < 0) {
+    const char* vr = getenv("BCP_VISIT_REV");
+    visit_rev = vr ? atoi(vr) : 1;
+  }
+  vo.rev = visit_rev;
   // k_solve: persistent, as many blocks as stay resident (shared-memory columns bound it)
   LaunchShape L = shape_for(P, N, false);
   // lane-major columns of float4: stride / 4 odd => conflict-free 16-byte accesses

@@ -264,12 +264,14 @@ struct VisitOrder {
   const int* cnt;   // [N_BINS]
   int* next_bins;   // filled by the closing kernel
   int* next_cnt;
+  int rev;          // walk the bins from the contact-rich regimes down (their blocks are the slow ones: first wave)
 };
 __device__ __forceinline__ int visit(const VisitOrder& vo, int i, int N) {
   if (!vo.cnt) return i < N ? i : -1;
   int at = i;
 #pragma unroll
-  for (int b = 0; b < N_BINS; ++b) {
+  for (int k = 0; k < N_BINS; ++k) {
+    const int b = vo.rev ? N_BINS - 1 - k : k;
     const int c = vo.cnt[b];
     if (at < c) return vo.bins[(size_t)b * N + at];
     at -= c;
