@@ -57,7 +57,8 @@ struct bcp_env {
     unsigned char* d_out = nullptr;  // obs f32[N][R][14] | reward f32[N] | done u8[N] | reason u8[N]
     float* d_slab = nullptr;         // [R][N][14]
     cudaStream_t copy = nullptr;
-    cudaEvent_t ev_ready = nullptr, ev_copied = nullptr;
+    cudaEvent_t ev_ready = nullptr, ev_copied = nullptr, ev_h2d = nullptr;
+    bool h2d_pending = false;        // the actions travel on the copy stream beside the first k_prep (which does not read them)
     float* h_obs = nullptr;          // this call's host slabs
     bool fired = false;
   } hs;
@@ -174,7 +175,7 @@ int bcp_destroy(bcp_env* h) {
   cudaFree(h->reward_sum); cudaFree(h->list); cudaFree(h->count); cudaFree(h->staging);
   if (h->hs.d_out) {
     cudaFree(h->hs.d_act); cudaFree(h->hs.d_out); cudaFree(h->hs.d_slab);
-    cudaStreamDestroy(h->hs.copy); cudaEventDestroy(h->hs.ev_ready); cudaEventDestroy(h->hs.ev_copied);
+    cudaStreamDestroy(h->hs.copy); cudaEventDestroy(h->hs.ev_ready); cudaEventDestroy(h->hs.ev_copied); if (h->hs.ev_h2d) cudaEventDestroy(h->hs.ev_h2d);
   }
   if (h->split.side) { cudaStreamDestroy(h->split.side); cudaEventDestroy(h->split.ev_prep); cudaEventDestroy(h->split.ev_gen); }
   cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc); cudaFree(h->split.cont); cudaFree(h->split.contm);
@@ -243,6 +244,10 @@ void pack_and_copy(bcp_env* h, int r, cudaStream_t s) {
 void host_step_hook(void* ctx, int k, cudaStream_t s) {
   bcp_env* h = static_cast<bcp_env*>(ctx);
   const int R = h->cfg.action_repeats, S = h->cfg.steps_per_repeat;
+  if (k == 0 && h->hs.h2d_pending) {
+    cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);  // every later kernel of the call reads the actions
+    h->hs.h2d_pending = false;
+  }
   if (k <= 0 || k >= R * S || k % S) return;  // the last repeat leaves with the call's other outputs
   cudaEventRecord(h->hs.ev_ready, s);
   cudaStreamWaitEvent(h->hs.copy, h->hs.ev_ready, 0);
@@ -272,18 +277,31 @@ int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_r
     }
     CK(cudaEventCreateWithFlags(&h->hs.ev_ready, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->hs.ev_copied, cudaEventDisableTiming));
+    CK(cudaEventCreateWithFlags(&h->hs.ev_h2d, cudaEventDisableTiming));
   }
   float* d_obs = reinterpret_cast<float*>(h->hs.d_out);
   float* d_rew = reinterpret_cast<float*>(h->hs.d_out + ob);
   uint8_t* d_done = h->hs.d_out + ob + rb;
   uint8_t* d_reason = d_done + n;
-  CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, s));
+  const bool split = !h->f64() && h->use_split;
+  if (split) {  // the first kernel of a split call (collision pass and rows of substep 0) does not depend on the actions
+    CK(cudaEventRecord(h->hs.ev_ready, s));
+    CK(cudaStreamWaitEvent(h->hs.copy, h->hs.ev_ready, 0));  // whatever read d_act before is done
+    CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, h->hs.copy));
+    CK(cudaEventRecord(h->hs.ev_h2d, h->hs.copy));
+    h->hs.h2d_pending = true;
+  } else {
+    CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, s));
+  }
   h->hs.h_obs = h_obs_rm;
   h->hs.fired = false;
-  const bool split = !h->f64() && h->use_split;
   if (split) { h->split.after_prep = host_step_hook; h->split.hook_ctx = h; }
   const int rc = bcp_step(h, h->hs.d_act, d_obs, d_rew, d_done, d_reason, stream);
   h->split.after_prep = nullptr;
+  if (h->hs.h2d_pending) {  // the call failed before its first kernel
+    cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);
+    h->hs.h2d_pending = false;
+  }
   if (rc) return rc;
   // the repeats that did not leave during the call (all of them on the one-launch pipeline)
   for (int r = h->hs.fired ? (int)R - 1 : 0; r < (int)R; ++r) pack_and_copy(h, r, s);
