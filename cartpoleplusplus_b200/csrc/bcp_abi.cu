@@ -270,6 +270,9 @@ int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_r
     CK(cudaMalloc(&h->hs.d_act, ab));
     CK(cudaMalloc((void**)&h->hs.d_out, ob + rb + 2 * n));
     CK(cudaMalloc((void**)&h->hs.d_slab, ob));
+    // an env that is mid-reset keeps its previous observation in the output block (bcp_step writes nothing there): start from zeros like the caller's own buffers
+    CK(cudaMemsetAsync(h->hs.d_out, 0, ob + rb + 2 * n, s));
+    CK(cudaMemsetAsync(h->hs.d_slab, 0, ob, s));
     {
       int lo = 0, hi = 0;
       cudaDeviceGetStreamPriorityRange(&lo, &hi);
