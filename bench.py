@@ -432,6 +432,26 @@ def run_reference(args):
     }))
 
 
+def ensure_built():
+    """The in-tree libraries are build products (git-ignored): compile them when a checkout arrives without
+    them.  One rank compiles, the others wait for the files."""
+    from cartpoleplusplus_b200 import _lib
+    from oracle.oracle import oracle_lib_path
+    need = [_lib.LIB_PATH, oracle_lib_path()]
+    if all(os.path.exists(p) for p in need):
+        return
+    if int(os.environ.get("LOCAL_RANK", "0")) == 0:
+        import __graft_entry__ as g
+        g.build()
+        return
+    t0 = time.time()
+    while not all(os.path.exists(p) for p in need):
+        if time.time() - t0 > 1800:
+            raise RuntimeError("timed out waiting for rank 0 to build libbcp.so")
+        time.sleep(2.0)
+    time.sleep(2.0)  # the linker's output is complete once the file is closed
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -449,6 +469,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    ensure_built()
     if args.impl == "reference":
         run_reference(args)
     else:
