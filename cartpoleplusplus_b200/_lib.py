@@ -16,7 +16,9 @@ EXPORTS = ["bcp_abi_version", "bcp_config_size", "bcp_last_error", "bcp_create",
            "bcp_replay_config_size", "bcp_replay_create", "bcp_replay_destroy", "bcp_replay_begin", "bcp_replay_observe",
            "bcp_replay_add_episode", "bcp_replay_batch", "bcp_replay_info", "bcp_replay_export", "bcp_replay_launch_count",
            # include/bcp_lqr.h
-           "bcp_lqr_args_size", "bcp_lqr_control"]
+           "bcp_lqr_args_size", "bcp_lqr_control",
+           # include/bcp_render.h
+           "bcp_render_args_size", "bcp_render_pixels"]
 
 REPLAY_ABI_VERSION = 1
 REPLAY_INFO_WORDS = 10
@@ -36,6 +38,19 @@ class BcpLqrArgs(ctypes.Structure):
                 ("x0", ctypes.c_void_p), ("disturbance", ctypes.c_void_p), ("disturbance_per_env", ctypes.c_int32),
                 ("position_threshold", ctypes.c_float), ("angle_threshold", ctypes.c_float),
                 ("state_out", ctypes.c_void_p), ("action_out", ctypes.c_void_p), ("done_out", ctypes.c_void_p)]
+
+
+class BcpRenderArgs(ctypes.Structure):
+    """mirror of bcp_render_args (include/bcp_render.h)"""
+    _f3 = ctypes.c_float * 3
+    _fields_ = [("num_envs", ctypes.c_int32), ("repeats", ctypes.c_int32), ("num_cameras", ctypes.c_int32),
+                ("width", ctypes.c_int32), ("height", ctypes.c_int32),
+                ("half_extents", (ctypes.c_float * 3) * 3), ("rgb", (ctypes.c_float * 3) * 3),
+                ("ground_pos", ctypes.c_float * 3), ("camera_pos", (ctypes.c_float * 3) * 2),
+                ("target", ctypes.c_float * 3), ("up", ctypes.c_float * 3),
+                ("near_val", ctypes.c_float), ("far_val", ctypes.c_float), ("fov_deg", ctypes.c_float), ("clip", ctypes.c_int32),
+                ("light_dir", ctypes.c_float * 3), ("ambient", ctypes.c_float), ("diffuse", ctypes.c_float),
+                ("background", ctypes.c_float * 3), ("obs", ctypes.c_void_p), ("pixels", ctypes.c_void_p)]
 
 
 class BcpError(RuntimeError):
@@ -90,6 +105,8 @@ def load(build_if_missing: bool = False):
     lib.bcp_replay_launch_count.argtypes = [vp]
     lib.bcp_replay_launch_count.restype = i64
     lib.bcp_lqr_args_size.restype = ctypes.c_size_t
+    lib.bcp_render_args_size.restype = ctypes.c_size_t
+    lib.bcp_render_pixels.argtypes = [ctypes.POINTER(BcpRenderArgs), ctypes.c_int, vp]
     lib.bcp_lqr_control.argtypes = [vp, ctypes.POINTER(BcpLqrArgs), vp]
     if lib.bcp_abi_version() != C.BCP_ABI_VERSION:
         raise BcpError(f"libbcp.so ABI {lib.bcp_abi_version()} != python mirror {C.BCP_ABI_VERSION}: rebuild")
@@ -99,6 +116,8 @@ def load(build_if_missing: bool = False):
         raise BcpError("sizeof(bcp_replay_config) differs between libbcp.so and the ctypes mirror: rebuild")
     if lib.bcp_lqr_args_size() != ctypes.sizeof(BcpLqrArgs):
         raise BcpError("sizeof(bcp_lqr_args) differs between libbcp.so and the ctypes mirror: rebuild")
+    if lib.bcp_render_args_size() != ctypes.sizeof(BcpRenderArgs):
+        raise BcpError("sizeof(bcp_render_args) differs between libbcp.so and the ctypes mirror: rebuild")
     _LIB = lib
     return lib
 

@@ -165,8 +165,6 @@ def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dt
     if g("num_cameras", 1) not in (1, 2):
         raise ValueError("--num-cameras must be 1 or 2")  # bullet_cartpole.py:113-114
     assert g("reward_calc", "fixed") in ["fixed", "angle", "action", "angle_action"]  # :144
-    if g("use_raw_pixels", False):
-        raise NotImplementedError("raw-pixel observations need pybullet's renderer: unavailable on this box")
     if g("gui", False):
         raise NotImplementedError("--gui needs a display: unavailable on this box")
     physics = physics or PhysicsParams()

@@ -42,6 +42,18 @@ class BatchedBulletCartpole:
         self.action_space = spaces.Discrete(5) if discrete_actions else spaces.Box(-1.0, 1.0, shape=(1, 2))
         float_max = np.finfo(np.float32).max
         self.observation_space = spaces.Box(-float_max, float_max, (self.repeats, 2, 7))
+        # --use-raw-pixels: the state is the (H, W, 3, C, R) image block (bullet_cartpole.py:96-101,299-306),
+        # ray-cast on the device from the poses of the call (render.py); env.obs keeps the poses
+        self.use_raw_pixels = bool(getattr(opts, "use_raw_pixels", False))
+        self._renderer = None
+        if self.use_raw_pixels:
+            from .render import PixelRenderer
+            from . import urdf as _urdf
+            scene = scene if scene is not None else _urdf.load_scene(getattr(opts, "model_dir", None))
+            self._renderer = PixelRenderer(self.cfg.num_envs, self.repeats, getattr(opts, "num_cameras", 1),
+                                           getattr(opts, "render_width", 50), getattr(opts, "render_height", 50),
+                                           scene=scene, device=self.device)
+            self.observation_space = spaces.Box(0.0, 1.0, self._renderer.state_shape)
         h = ctypes.c_void_p()
         _lib.check(self._lib.bcp_create(ctypes.byref(self.cfg), ctypes.byref(h)), self._lib)
         self._h = h
@@ -98,6 +110,12 @@ class BatchedBulletCartpole:
         else:
             self.done.masked_fill_(mask.bool(), 0)
         self._was_reset = True
+        return self._state(copy)
+
+    def _state(self, copy: bool) -> torch.Tensor:
+        if self._renderer is not None:
+            px = self._renderer.render(self.obs)
+            return px.clone() if copy else px
         return self.obs.clone() if copy else self.obs
 
     # ---- step, bullet_cartpole.py:178-275 ----
@@ -128,8 +146,8 @@ class BatchedBulletCartpole:
                                       ctypes.c_void_p(self.reason.data_ptr()), self._stream()), self._lib)
         info = {"done_reason": self.reason.clone() if copy else self.reason}
         if copy:
-            return self.obs.clone(), self.reward.clone(), self.done.bool(), info
-        return self.obs, self.reward, self.done.view(torch.bool), info  # 0/1 bytes: a view, no kernel
+            return self._state(True), self.reward.clone(), self.done.bool(), info
+        return self._state(False), self.reward, self.done.view(torch.bool), info  # 0/1 bytes: a view, no kernel
 
     # ---- host-buffer call: what a CPU-side agent loop uses (pinned buffers, one sync) ----
     def step_host(self, actions_host: torch.Tensor, auto_reset: bool = False):
@@ -141,6 +159,8 @@ class BatchedBulletCartpole:
         auto_reset=True (reset(mask=done) after the step, so that the next observation of a finished
         env is its reset observation) takes the plain path: step, one D2H, reset."""
         n, R = self.num_envs, self.repeats
+        if self._renderer is not None:
+            raise _lib.BcpError("step_host moves the low-dimensional observation; with --use-raw-pixels use step()")
         if not hasattr(self, "_h_out"):
             ob, rb = self.obs.numel() * 4, n * 4
             self._h_out = torch.empty(self._out.numel(), dtype=torch.uint8).pin_memory()

@@ -40,6 +40,7 @@ class BoxBody:
     rolling_friction: float = 0.0
     contact_cfm: Optional[float] = None
     contact_erp: Optional[float] = None
+    rgba: Tuple[float, float, float, float] = (1.0, 1.0, 1.0, 1.0)  # <visual><material><color rgba>: the pixel observation's colours
 
     @property
     def half_extents(self) -> Tuple[float, float, float]:
@@ -98,6 +99,8 @@ def parse_box_urdf(path: str) -> BoxBody:
     if len(size) != 3:
         raise ValueError(f"{path}: box size needs 3 values")
     contact = link.find("contact")
+    color = link.find("visual/material/color")
+    rgba = tuple(float(v) for v in color.attrib["rgba"].split()) if color is not None and "rgba" in color.attrib else (1.0, 1.0, 1.0, 1.0)
     return BoxBody(
         name=root.attrib.get("name", os.path.basename(path)),
         mass=mass,
@@ -109,6 +112,7 @@ def parse_box_urdf(path: str) -> BoxBody:
         rolling_friction=_value(contact, "rolling_friction", 0.0),
         contact_cfm=_value(contact, "contact_cfm"),
         contact_erp=_value(contact, "contact_erp"),
+        rgba=rgba,
     )
 
 

@@ -67,7 +67,8 @@ def test_config_errors_mirror_reference():
     with pytest.raises(AssertionError):  # :144
         make_config(default_opts(reward_calc="bogus"), True)
     with pytest.raises(NotImplementedError):
-        make_config(default_opts(use_raw_pixels=True), True)
+        make_config(default_opts(gui=True), True)
+    make_config(default_opts(use_raw_pixels=True), True)  # the pixel observation is rendered by the env (render.py)
     with pytest.raises(ValueError):
         make_config(default_opts(action_repeats=0), True)
     with pytest.raises(ValueError):
