@@ -22,7 +22,7 @@ UNITS = [
     ("bcp_f64.cu", ["-fmad=false"]),
     ("bcp_abi.cu", []),
     ("bcp_replay.cu", []),
-    ("bcp_render.cu", []),
+    ("bcp_render.cu", ["-prec-div=false"]),
 ]
 
 
