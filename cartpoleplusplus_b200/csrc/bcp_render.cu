@@ -73,8 +73,9 @@ __device__ __forceinline__ __half to_pixel(float v) {
   return __float2half_rn((float)u8 / 255.f);
 }
 // What a pixel sees when neither cart nor pole is in the way does not depend on the env: its ray, the
-// ground hit and the finished colour are worked out once per (camera, pixel) ...
-__global__ void k_render_table(const Scene sc, float4* __restrict__ rays, float* __restrict__ depth, __half* __restrict__ base) {
+// ground hit and the finished colour are worked out once per (camera, pixel); `img` is that background
+// already in the reference's layout, [pixel][3][C][R] ...
+__global__ void k_render_table(const Scene sc, float4* __restrict__ rays, float* __restrict__ depth, __half* __restrict__ img) {
   const int npix = sc.W * sc.H, i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= sc.C * npix) return;
   const int c = i / npix, pix = i - c * npix;
@@ -89,27 +90,31 @@ __global__ void k_render_table(const Scene sc, float4* __restrict__ rays, float*
   for (int k = 0; k < 9; ++k) ground.ax[k] = (k % 4 == 0) ? 1.f : 0.f;
   float best = sc.far_val, n[3] = {0.f, 0.f, 0.f};
   const bool hit = ray_box(cam.eye, d, ground, sc.h[0], sc.near_val, sc.far_val, best, n);
-  rays[i] = make_float4(d[0], d[1], d[2], 1.f / (d[0] * d[0] + d[1] * d[1] + d[2] * d[2]));
+  rays[i] = make_float4(d[0], d[1], d[2], 0.f);
   depth[i] = best;
   const float shade = hit ? sc.ambient + sc.diffuse * fmaxf(0.f, n[0] * sc.light[0] + n[1] * sc.light[1] + n[2] * sc.light[2]) : 1.f;
-  for (int ch = 0; ch < 3; ++ch) base[(size_t)i * 3 + ch] = to_pixel(hit ? sc.rgb[0][ch] * shade : sc.bg[ch]);
+  const int CR = sc.C * sc.R;
+  for (int ch = 0; ch < 3; ++ch) {
+    const __half v = to_pixel(hit ? sc.rgb[0][ch] * shade : sc.bg[ch]);
+    for (int r = 0; r < sc.R; ++r) img[((size_t)pix * 3 + ch) * CR + c * sc.R + r] = v;
+  }
 }
 
-// ... and the per-env kernel only tests the two moving boxes, behind a screen-space bounding rectangle per
-// (camera, repeat, box): the corners are projected once per env, most pixels fail four integer compares and
-// take the table's colour.  One block per env; after the set-up its warps are independent: a warp renders 32
-// consecutive pixels at a time and writes their 32 * 3*C*R halves, contiguous in the reference's layout,
-// with the widest stores the alignment allows.
-constexpr int kWarps = kThreads / 32;
-struct Rect { int x0, x1, y0, y1; };
+// ... and the per-env kernel, one block per env, (1) streams that background into the env's block with the
+// widest stores the alignment allows and (2) re-renders only the pixels inside the screen rectangles of the
+// cart and the pole of each (camera, repeat) - the eight corners of a box projected once - as a flat list of
+// (rectangle, pixel) tasks spread over the block, so that the few hundred rays that can hit something do not
+// drag whole warps of background pixels through the intersection code.
+struct Rect { int x0, y0, w, h; };
+constexpr int kMaxRects = 2 * kMaxR * 2;
 __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float* __restrict__ obs, const float4* __restrict__ rays,
-                                                     const float* __restrict__ depth, const __half* __restrict__ base,
+                                                     const float* __restrict__ depth, const __half* __restrict__ img,
                                                      __half* __restrict__ out) {
   __shared__ Box box[kMaxR][2];
-  __shared__ Rect rect[2][kMaxR][2];  // [camera][repeat][cart, pole]
-  __shared__ __align__(16) __half stage_all[kWarps][32 * 3 * 2 * kMaxR];
-  const int env = blockIdx.x, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int npix = sc.W * sc.H, CR = sc.C * sc.R;
+  __shared__ Rect rect[kMaxRects];      // index (c * R + r) * 2 + body
+  __shared__ int first[kMaxRects + 1];  // prefix of the rectangles' pixel counts
+  const int env = blockIdx.x;
+  const int npix = sc.W * sc.H, CR = sc.C * sc.R, nrect = CR * 2;
   if (threadIdx.x < sc.R * 2) {
     const int r = threadIdx.x >> 1, body = threadIdx.x & 1;
     const float* p = obs + (((size_t)env * sc.R + r) * 2 + body) * 7;
@@ -117,8 +122,22 @@ __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float
     b.c[0] = p[0]; b.c[1] = p[1]; b.c[2] = p[2];
     quat_axes(p + 3, b.ax);
   }
+  // (1) the background, while the poses arrive
+  {
+    const size_t nbytes = (size_t)npix * 3 * CR * sizeof(__half);
+    char* g = reinterpret_cast<char*>(out + (size_t)env * npix * 3 * CR);
+    const char* src = reinterpret_cast<const char*>(img);
+    const size_t al = reinterpret_cast<size_t>(g) | reinterpret_cast<size_t>(src) | nbytes;
+    if ((al & 15) == 0) {
+      for (size_t i = threadIdx.x; i < nbytes / 16; i += kThreads) reinterpret_cast<uint4*>(g)[i] = reinterpret_cast<const uint4*>(src)[i];
+    } else if ((al & 3) == 0) {
+      for (size_t i = threadIdx.x; i < nbytes / 4; i += kThreads) reinterpret_cast<uint32_t*>(g)[i] = reinterpret_cast<const uint32_t*>(src)[i];
+    } else {
+      for (size_t i = threadIdx.x; i < nbytes / 2; i += kThreads) reinterpret_cast<uint16_t*>(g)[i] = reinterpret_cast<const uint16_t*>(src)[i];
+    }
+  }
   __syncthreads();
-  if (threadIdx.x < sc.C * sc.R * 2) {  // screen rectangle of one box in one image: its eight corners projected
+  if (threadIdx.x < nrect) {  // screen rectangle of one box in one image: its eight corners projected
     const int c = threadIdx.x / (sc.R * 2), rb = threadIdx.x - c * sc.R * 2, r = rb >> 1, body = rb & 1;
     const Camera& cam = sc.cam[c];
     const Box& b = box[r][body];
@@ -136,60 +155,45 @@ __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float
       const float fx = (x + 1.f) * 0.5f * (float)sc.W - 0.5f, fy = (1.f - y) * 0.5f * (float)sc.H - 0.5f;  // pixel-centre coordinates
       xmin = fminf(xmin, fx); xmax = fmaxf(xmax, fx); ymin = fminf(ymin, fy); ymax = fmaxf(ymax, fy);
     }
-    Rect q;
-    if (all || !(xmax - xmin < 1e6f)) { q.x0 = 0; q.x1 = sc.W - 1; q.y0 = 0; q.y1 = sc.H - 1; }
-    else {  // one pixel of slack against rounding
-      q.x0 = (int)floorf(fmaxf(xmin, -2.f)) - 1; q.x1 = (int)ceilf(fminf(xmax, (float)sc.W + 2.f)) + 1;
-      q.y0 = (int)floorf(fmaxf(ymin, -2.f)) - 1; q.y1 = (int)ceilf(fminf(ymax, (float)sc.H + 2.f)) + 1;
+    int x0 = 0, x1 = sc.W - 1, y0 = 0, y1 = sc.H - 1;
+    if (!all && xmax - xmin < 1e6f && ymax - ymin < 1e6f) {  // one pixel of slack against rounding, clamped to the image
+      x0 = max(0, (int)floorf(fmaxf(xmin, -2.f)) - 1); x1 = min(sc.W - 1, (int)ceilf(fminf(xmax, (float)sc.W + 2.f)) + 1);
+      y0 = max(0, (int)floorf(fmaxf(ymin, -2.f)) - 1); y1 = min(sc.H - 1, (int)ceilf(fminf(ymax, (float)sc.H + 2.f)) + 1);
     }
-    rect[c][r][body] = q;
+    Rect q;
+    q.x0 = x0; q.y0 = y0; q.w = max(0, x1 - x0 + 1); q.h = max(0, y1 - y0 + 1);
+    rect[threadIdx.x] = q;
   }
   __syncthreads();
-  __half* stage = stage_all[warp];
-  for (int pix0 = warp * 32; pix0 < npix; pix0 += kThreads) {
-    const int pix = pix0 + lane;
-    if (pix < npix) {
-      const int py = pix / sc.W, px = pix - py * sc.W;
-      __half* dst = stage + (size_t)lane * 3 * CR;
-      for (int c = 0; c < sc.C; ++c) {
-        const Camera& cam = sc.cam[c];
-        const __half* bc = base + (size_t)(c * npix + pix) * 3;
-        const __half b0 = bc[0], b1 = bc[1], b2 = bc[2];
-        for (int r = 0; r < sc.R; ++r) {
-          __half v0 = b0, v1 = b1, v2 = b2;
-          const Rect q0 = rect[c][r][0], q1 = rect[c][r][1];
-          const bool in0 = px >= q0.x0 && px <= q0.x1 && py >= q0.y0 && py <= q0.y1;
-          const bool in1 = px >= q1.x0 && px <= q1.x1 && py >= q1.y0 && py <= q1.y1;
-          if (in0 || in1) {
-            const float4 ray = rays[c * npix + pix];
-            const float d[3] = {ray.x, ray.y, ray.z};
-            float best = depth[c * npix + pix], n[3] = {0.f, 0.f, 0.f};
-            int body = 0;
-            if (in0 && ray_box(cam.eye, d, box[r][0], sc.h[1], sc.near_val, sc.far_val, best, n)) body = 1;
-            if (in1 && ray_box(cam.eye, d, box[r][1], sc.h[2], sc.near_val, sc.far_val, best, n)) body = 2;
-            if (body) {
-              const float shade = sc.ambient + sc.diffuse * fmaxf(0.f, n[0] * sc.light[0] + n[1] * sc.light[1] + n[2] * sc.light[2]);
-              v0 = to_pixel(sc.rgb[body][0] * shade); v1 = to_pixel(sc.rgb[body][1] * shade); v2 = to_pixel(sc.rgb[body][2] * shade);
-            }
-          }
-          dst[c * sc.R + r] = v0; dst[CR + c * sc.R + r] = v1; dst[2 * CR + c * sc.R + r] = v2;
-        }
-      }
-    }
-    __syncwarp();
-    const int live = min(32, npix - pix0);
-    const unsigned nbytes = (unsigned)(live * 3 * CR * sizeof(__half));
-    char* g = reinterpret_cast<char*>(out + ((size_t)env * npix + pix0) * 3 * CR);
-    const char* sm = reinterpret_cast<const char*>(stage);
-    const size_t al = reinterpret_cast<size_t>(g) | nbytes;
-    if ((al & 15) == 0) {
-      for (unsigned i = lane; i < nbytes / 16; i += 32) reinterpret_cast<uint4*>(g)[i] = reinterpret_cast<const uint4*>(sm)[i];
-    } else if ((al & 3) == 0) {
-      for (unsigned i = lane; i < nbytes / 4; i += 32) reinterpret_cast<uint32_t*>(g)[i] = reinterpret_cast<const uint32_t*>(sm)[i];
-    } else {
-      for (unsigned i = lane; i < nbytes / 2; i += 32) reinterpret_cast<uint16_t*>(g)[i] = reinterpret_cast<const uint16_t*>(sm)[i];
-    }
-    __syncwarp();  // the slice is reused by the warp's next 32 pixels
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int k = 0; k < nrect; ++k) { first[k] = acc; acc += rect[k].w * rect[k].h; }
+    first[nrect] = acc;
+  }
+  __syncthreads();
+  // (2) the pixels a box can cover
+  const int total = first[nrect];
+  for (int t = threadIdx.x; t < total; t += kThreads) {
+    int k = 0;
+    while (t >= first[k + 1]) ++k;
+    const Rect q = rect[k];
+    const int local = t - first[k], ly = local / q.w, px = q.x0 + (local - ly * q.w), py = q.y0 + ly;
+    const int cr = k >> 1, c = cr / sc.R, r = cr - c * sc.R, mine = k & 1;
+    const Rect o = rect[k ^ 1];  // the other box of the same image
+    const bool in_other = px >= o.x0 && px < o.x0 + o.w && py >= o.y0 && py < o.y0 + o.h;
+    if (in_other && mine == 1) continue;  // the cart's task renders the shared pixel
+    const Camera& cam = sc.cam[c];
+    const int pix = py * sc.W + px;
+    const float4 ray = rays[c * npix + pix];
+    const float d[3] = {ray.x, ray.y, ray.z};
+    float best = depth[c * npix + pix], n[3] = {0.f, 0.f, 0.f};
+    int body = 0;
+    if ((mine == 0 || in_other) && ray_box(cam.eye, d, box[r][0], sc.h[1], sc.near_val, sc.far_val, best, n)) body = 1;
+    if ((mine == 1 || in_other) && ray_box(cam.eye, d, box[r][1], sc.h[2], sc.near_val, sc.far_val, best, n)) body = 2;
+    if (!body) continue;  // the background is already there
+    const float shade = sc.ambient + sc.diffuse * fmaxf(0.f, n[0] * sc.light[0] + n[1] * sc.light[1] + n[2] * sc.light[2]);
+    __half* dst = out + ((size_t)env * npix + pix) * 3 * CR + c * sc.R + r;
+    dst[0] = to_pixel(sc.rgb[body][0] * shade); dst[CR] = to_pixel(sc.rgb[body][1] * shade); dst[2 * CR] = to_pixel(sc.rgb[body][2] * shade);
   }
 }
 
@@ -240,7 +244,7 @@ int bcp_render_pixels(const bcp_render_args* a, int device_ordinal, void* stream
   if (prev != device_ordinal) cudaSetDevice(device_ordinal);
   cudaStream_t st = (cudaStream_t)stream;
   const size_t nt = (size_t)sc.C * a->width * a->height;
-  // per-call scratch from the stream-ordered pool: rays f32x4 | ground depth f32 | base colour f16x3
+  // per-call scratch from the stream-ordered pool: rays f32x4 | ground depth f32 | background image f16
   char* scratch = nullptr;
   {  // keep freed scratch in the device's default pool across synchronisations (the default gives it back to the driver)
     static bool pool_set[64] = {false};
@@ -253,14 +257,14 @@ int bcp_render_pixels(const bcp_render_args* a, int device_ordinal, void* stream
       pool_set[device_ordinal] = true;
     }
   }
-  cudaError_t e0 = cudaMallocAsync((void**)&scratch, nt * (16 + 4 + 8), st);
+  cudaError_t e0 = cudaMallocAsync((void**)&scratch, nt * (16 + 4) + 16 + nt * 3 * (size_t)sc.R * sizeof(__half), st);
   if (e0 != cudaSuccess) {
     if (prev != device_ordinal) cudaSetDevice(prev);
     return bcp::abi_fail("bcp_render_pixels: scratch allocation", e0);
   }
   float4* rays = reinterpret_cast<float4*>(scratch);
   float* depth = reinterpret_cast<float*>(scratch + nt * 16);
-  __half* base = reinterpret_cast<__half*>(scratch + nt * 20);
+  __half* base = reinterpret_cast<__half*>(scratch + (nt * 20 + 15) / 16 * 16);  // [pixel][3][C][R], 16-byte aligned
   k_render_table<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(sc, rays, depth, base);
   const dim3 grid((unsigned)a->num_envs, 1);
   k_render<<<grid, kThreads, 0, st>>>(sc, a->obs, rays, depth, base, reinterpret_cast<__half*>(a->pixels));

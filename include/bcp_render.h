@@ -2,8 +2,9 @@
  *
  * Replaces bullet_cartpole.py:277-296 (render_rgb: p.renderImage at render_width x render_height from one
  * of two fixed cameras, uint8 RGBA -> float16 / 255) and :299-306 (state[:, :, :, camera, repeat]) for a
- * whole batch: one launch turns the low-dimensional observation of a call - the (R, 2, 7) cart and pole
- * poses per env that bcp_step / bcp_reset wrote - into the (H, W, 3, C, R) float16 image block per env.
+ * whole batch: one call (a small per-pixel table kernel, then one block per env) turns the low-dimensional
+ * observation of a step - the (R, 2, 7) cart and pole poses per env that bcp_step / bcp_reset wrote - into
+ * the (H, W, 3, C, R) float16 image block per env.
  * No window, no graphics API: three boxes (ground, cart, pole) are ray-cast per pixel from pybullet's
  * camera model (computeViewMatrix + computeProjectionMatrixFOV, restated in DESIGN.md section 12).
  *
@@ -46,7 +47,8 @@ typedef struct bcp_render_args {
 
 size_t bcp_render_args_size(void);
 
-/* One launch on `stream` of device `device_ordinal`.  Returns 0, or -1 with bcp_last_error() set. */
+/* Enqueued on `stream` of device `device_ordinal` (scratch comes from the device's stream-ordered pool).
+ * Returns 0, or -1 with bcp_last_error() set. */
 int bcp_render_pixels(const bcp_render_args* args, int device_ordinal, void* stream);
 
 #ifdef __cplusplus
