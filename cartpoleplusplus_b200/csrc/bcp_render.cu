@@ -156,9 +156,11 @@ __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float
       xmin = fminf(xmin, fx); xmax = fmaxf(xmax, fx); ymin = fminf(ymin, fy); ymax = fmaxf(ymax, fy);
     }
     int x0 = 0, x1 = sc.W - 1, y0 = 0, y1 = sc.H - 1;
-    if (!all && xmax - xmin < 1e6f && ymax - ymin < 1e6f) {  // one pixel of slack against rounding, clamped to the image
-      x0 = max(0, (int)floorf(fmaxf(xmin, -2.f)) - 1); x1 = min(sc.W - 1, (int)ceilf(fminf(xmax, (float)sc.W + 2.f)) + 1);
-      y0 = max(0, (int)floorf(fmaxf(ymin, -2.f)) - 1); y1 = min(sc.H - 1, (int)ceilf(fminf(ymax, (float)sc.H + 2.f)) + 1);
+    if (!all && xmax - xmin < 1e6f && ymax - ymin < 1e6f) {
+      // pixel centres inside the projected hull's bounds (a convex box projects inside the bounds of its corners);
+      // 0.05 pixel of slack against rounding, clamped to the image
+      x0 = max(0, (int)ceilf(fmaxf(xmin, -2.f) - 0.05f)); x1 = min(sc.W - 1, (int)floorf(fminf(xmax, (float)sc.W + 2.f) + 0.05f));
+      y0 = max(0, (int)ceilf(fmaxf(ymin, -2.f) - 0.05f)); y1 = min(sc.H - 1, (int)floorf(fminf(ymax, (float)sc.H + 2.f) + 0.05f));
     }
     Rect q;
     q.x0 = x0; q.y0 = y0; q.w = max(0, x1 - x0 + 1); q.h = max(0, y1 - y0 + 1);

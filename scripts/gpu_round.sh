@@ -36,3 +36,5 @@ except Exception as e:
     print(sys.argv[1], 'unreadable', e)
 PY
 done
+timeout 300 python scripts/bench_render.py > $O/${TAG}_render_bench.json 2> $O/${TAG}_render_bench.err
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_render$ -s 2 -c 1 -f -o $O/${TAG}_k_render python scripts/bench_render.py --reps 3 > $O/${TAG}_ncu_render.log 2>&1
