@@ -105,7 +105,7 @@ __global__ void k_render_table(const Scene sc, float4* __restrict__ rays, float*
 // cart and the pole of each (camera, repeat) - the eight corners of a box projected once - as a flat list of
 // (rectangle, pixel) tasks spread over the block, so that the few hundred rays that can hit something do not
 // drag whole warps of background pixels through the intersection code.
-struct Rect { int x0, y0, w, h; };
+struct Rect { int x0, y0, w, h, c, r; float inv_w; };  // inv_w: row of a task without an integer division
 constexpr int kMaxRects = 2 * kMaxR * 2;
 __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float* __restrict__ obs, const float4* __restrict__ rays,
                                                      const float* __restrict__ depth, const __half* __restrict__ img,
@@ -164,6 +164,7 @@ __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float
     }
     Rect q;
     q.x0 = x0; q.y0 = y0; q.w = max(0, x1 - x0 + 1); q.h = max(0, y1 - y0 + 1);
+    q.c = c; q.r = r; q.inv_w = 1.f / (float)max(1, q.w);
     rect[threadIdx.x] = q;
   }
   __syncthreads();
@@ -179,8 +180,12 @@ __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float
     int k = 0;
     while (t >= first[k + 1]) ++k;
     const Rect q = rect[k];
-    const int local = t - first[k], ly = local / q.w, px = q.x0 + (local - ly * q.w), py = q.y0 + ly;
-    const int cr = k >> 1, c = cr / sc.R, r = cr - c * sc.R, mine = k & 1;
+    const int local = t - first[k];
+    int ly = (int)(((float)local + 0.5f) * q.inv_w);  // local < 2^15: exact up to the rounding of inv_w, fixed below
+    ly -= (ly * q.w > local);
+    ly += ((ly + 1) * q.w <= local);
+    const int px = q.x0 + (local - ly * q.w), py = q.y0 + ly;
+    const int c = q.c, r = q.r, mine = k & 1;
     const Rect o = rect[k ^ 1];  // the other box of the same image
     const bool in_other = px >= o.x0 && px < o.x0 + o.w && py >= o.y0 && py < o.y0 + o.h;
     if (in_other && mine == 1) continue;  // the cart's task renders the shared pixel
