@@ -1,8 +1,8 @@
-run() { timeout 600 python bench.py --steps 20 --warmup 3 --no-cpu-baseline $2 2>/dev/null | python -c "import sys,json; d=json.loads(sys.stdin.read().strip().splitlines()[-1]); print('$1', d['value'], d['kernel_ms_per_step'], d['e2e']['value'])"; }
-run "base 65536" ""
-BCP_PREP_BLOCK=64 run "block64 65536" ""
-BCP_PREP_BLOCK=96 run "block96 65536" ""
-BCP_NVCC_EXTRA="-DBCP_PREP_MINB=3" python -c "from cartpoleplusplus_b200 import build; build.build(force=True)"
-grep -A2 "k_prepIfLb1" cartpoleplusplus_b200/csrc/build/bcp_f32.o.ptxas.log | tail -2 | cut -c1-200
-run "minb3 65536" ""
-run "minb3 262144" "--envs 262144"
+mkdir -p gpurun_out
+N=${1:-2}
+TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511"
+timeout 600 $TR bench.py --impl reference --gpus $N --steps 5 --warmup 1 > gpurun_out/r1_v10_bench_${N}gpu_reference.json 2> gpurun_out/r1_v10_bench_${N}gpu_reference.err
+timeout 600 $TR bench.py --gpus $N --no-cpu-baseline > gpurun_out/r1_v10_bench_${N}gpu.json 2> gpurun_out/r1_v10_bench_${N}gpu.err
+tail -2 gpurun_out/r1_v10_bench_${N}gpu.err
+for f in gpurun_out/r1_v10_bench_${N}gpu.json gpurun_out/r1_v10_bench_${N}gpu_reference.json; do python -c "
+import json,sys; d=json.loads(open('$f').read().strip().splitlines()[-1]); print('$f', d['value'], d['n_gpus'], d['e2e']['value'], d['ms_per_step'], d.get('clocks'))"; done
