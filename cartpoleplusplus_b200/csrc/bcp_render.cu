@@ -137,41 +137,60 @@ __global__ void __launch_bounds__(kThreads) k_render(const Scene sc, const float
     }
   }
   __syncthreads();
-  if (threadIdx.x < nrect) {  // screen rectangle of one box in one image: its eight corners projected
-    const int c = threadIdx.x / (sc.R * 2), rb = threadIdx.x - c * sc.R * 2, r = rb >> 1, body = rb & 1;
-    const Camera& cam = sc.cam[c];
-    const Box& b = box[r][body];
-    const float* h = sc.h[1 + body];
-    float xmin = 1e30f, xmax = -1e30f, ymin = 1e30f, ymax = -1e30f;
-    bool all = false;
-    for (int k = 0; k < 8; ++k) {
-      const float sx = (k & 1) ? h[0] : -h[0], sy = (k & 2) ? h[1] : -h[1], sz = (k & 4) ? h[2] : -h[2];
+  // screen rectangle of one box in one image: its eight corners projected, one corner per lane, four
+  // rectangles per warp at a time
+  {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, corner = lane & 7;
+    for (int k0 = warp * 4; k0 < nrect; k0 += kThreads / 32 * 4) {
+      const int k = k0 + (lane >> 3), kk = min(k, nrect - 1);
+      const int cr = kk >> 1, body = kk & 1, c = cr / sc.R, r = cr - c * sc.R;
+      const Camera& cam = sc.cam[c];
+      const Box& b = box[r][body];
+      const float* h = sc.h[1 + body];
+      const float sx = (corner & 1) ? h[0] : -h[0], sy = (corner & 2) ? h[1] : -h[1], sz = (corner & 4) ? h[2] : -h[2];
       float p[3];
       for (int i = 0; i < 3; ++i) p[i] = b.c[i] + sx * b.ax[i] + sy * b.ax[3 + i] + sz * b.ax[6 + i] - cam.eye[i];
       const float z = p[0] * cam.f[0] + p[1] * cam.f[1] + p[2] * cam.f[2];
-      if (!(z > 1e-3f)) { all = true; break; }  // a corner at or behind the eye: no useful bound
-      const float x = (p[0] * cam.s[0] + p[1] * cam.s[1] + p[2] * cam.s[2]) / (z * cam.tx);
-      const float y = (p[0] * cam.u[0] + p[1] * cam.u[1] + p[2] * cam.u[2]) / (z * cam.ty);
+      const bool bad = !(z > 1e-3f);  // a corner at or behind the eye: no useful bound
+      const float zz = bad ? 1.f : z;
+      const float x = (p[0] * cam.s[0] + p[1] * cam.s[1] + p[2] * cam.s[2]) / (zz * cam.tx);
+      const float y = (p[0] * cam.u[0] + p[1] * cam.u[1] + p[2] * cam.u[2]) / (zz * cam.ty);
       const float fx = (x + 1.f) * 0.5f * (float)sc.W - 0.5f, fy = (1.f - y) * 0.5f * (float)sc.H - 0.5f;  // pixel-centre coordinates
-      xmin = fminf(xmin, fx); xmax = fmaxf(xmax, fx); ymin = fminf(ymin, fy); ymax = fmaxf(ymax, fy);
+      float xmin = fx, xmax = fx, ymin = fy, ymax = fy;
+      int all = bad ? 1 : 0;
+#pragma unroll
+      for (int o = 1; o < 8; o <<= 1) {
+        xmin = fminf(xmin, __shfl_xor_sync(0xffffffffu, xmin, o)); xmax = fmaxf(xmax, __shfl_xor_sync(0xffffffffu, xmax, o));
+        ymin = fminf(ymin, __shfl_xor_sync(0xffffffffu, ymin, o)); ymax = fmaxf(ymax, __shfl_xor_sync(0xffffffffu, ymax, o));
+        all |= __shfl_xor_sync(0xffffffffu, all, o);
+      }
+      if (corner == 0 && k < nrect) {
+        int x0 = 0, x1 = sc.W - 1, y0 = 0, y1 = sc.H - 1;
+        if (!all && xmax - xmin < 1e6f && ymax - ymin < 1e6f) {
+          // pixel centres inside the projected hull's bounds (a convex box projects inside the bounds of its corners);
+          // 0.05 pixel of slack against rounding, clamped to the image
+          x0 = max(0, (int)ceilf(fmaxf(xmin, -2.f) - 0.05f)); x1 = min(sc.W - 1, (int)floorf(fminf(xmax, (float)sc.W + 2.f) + 0.05f));
+          y0 = max(0, (int)ceilf(fmaxf(ymin, -2.f) - 0.05f)); y1 = min(sc.H - 1, (int)floorf(fminf(ymax, (float)sc.H + 2.f) + 0.05f));
+        }
+        Rect q;
+        q.x0 = x0; q.y0 = y0; q.w = max(0, x1 - x0 + 1); q.h = max(0, y1 - y0 + 1);
+        q.c = c; q.r = r; q.inv_w = 1.f / (float)max(1, q.w);
+        rect[k] = q;
+      }
     }
-    int x0 = 0, x1 = sc.W - 1, y0 = 0, y1 = sc.H - 1;
-    if (!all && xmax - xmin < 1e6f && ymax - ymin < 1e6f) {
-      // pixel centres inside the projected hull's bounds (a convex box projects inside the bounds of its corners);
-      // 0.05 pixel of slack against rounding, clamped to the image
-      x0 = max(0, (int)ceilf(fmaxf(xmin, -2.f) - 0.05f)); x1 = min(sc.W - 1, (int)floorf(fminf(xmax, (float)sc.W + 2.f) + 0.05f));
-      y0 = max(0, (int)ceilf(fmaxf(ymin, -2.f) - 0.05f)); y1 = min(sc.H - 1, (int)floorf(fminf(ymax, (float)sc.H + 2.f) + 0.05f));
-    }
-    Rect q;
-    q.x0 = x0; q.y0 = y0; q.w = max(0, x1 - x0 + 1); q.h = max(0, y1 - y0 + 1);
-    q.c = c; q.r = r; q.inv_w = 1.f / (float)max(1, q.w);
-    rect[threadIdx.x] = q;
   }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    int acc = 0;
-    for (int k = 0; k < nrect; ++k) { first[k] = acc; acc += rect[k].w * rect[k].h; }
-    first[nrect] = acc;
+  if (threadIdx.x < 32) {  // exclusive prefix of the rectangles' pixel counts (nrect <= 32): one warp scan
+    const int lane = threadIdx.x;
+    const int area = lane < nrect ? rect[lane].w * rect[lane].h : 0;
+    int inc = area;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int v = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += v;
+    }
+    if (lane < nrect) first[lane] = inc - area;
+    if (lane == nrect - 1) first[nrect] = inc;
   }
   __syncthreads();
   // (2) the pixels a box can cover
