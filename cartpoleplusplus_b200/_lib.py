@@ -18,7 +18,7 @@ EXPORTS = ["bcp_abi_version", "bcp_config_size", "bcp_last_error", "bcp_create",
            # include/bcp_lqr.h
            "bcp_lqr_args_size", "bcp_lqr_control",
            # include/bcp_render.h
-           "bcp_render_args_size", "bcp_render_pixels"]
+           "bcp_render_args_size", "bcp_render_pixels", "bcp_render_static_scratch_bytes", "bcp_render_pixels_static"]
 
 REPLAY_ABI_VERSION = 1
 REPLAY_INFO_WORDS = 10
@@ -107,6 +107,8 @@ def load(build_if_missing: bool = False):
     lib.bcp_lqr_args_size.restype = ctypes.c_size_t
     lib.bcp_render_args_size.restype = ctypes.c_size_t
     lib.bcp_render_pixels.argtypes = [ctypes.POINTER(BcpRenderArgs), ctypes.c_int, vp]
+    lib.bcp_render_static_scratch_bytes.restype = ctypes.c_size_t
+    lib.bcp_render_pixels_static.argtypes = [ctypes.POINTER(BcpRenderArgs), ctypes.c_int, vp]
     lib.bcp_lqr_control.argtypes = [vp, ctypes.POINTER(BcpLqrArgs), vp]
     if lib.bcp_abi_version() != C.BCP_ABI_VERSION:
         raise BcpError(f"libbcp.so ABI {lib.bcp_abi_version()} != python mirror {C.BCP_ABI_VERSION}: rebuild")

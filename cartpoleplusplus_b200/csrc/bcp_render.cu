@@ -6,6 +6,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdio.h>
 
 #include "../../include/bcp_render.h"
 
@@ -298,6 +299,109 @@ int bcp_render_pixels(const bcp_render_args* a, int device_ordinal, void* stream
   const cudaError_t e = cudaGetLastError();
   if (prev != device_ordinal) cudaSetDevice(prev);
   if (e != cudaSuccess) return bcp::abi_fail("bcp_render_pixels: launch", e);
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- bcp_render_pixels_static: the same two kernels with NO allocation anywhere on the call path ----
+// (include/bcp_render.h; no counterpart in the reference).  The per-call scratch of bcp_render_pixels -
+// rays | ground depth | background image - lives in a file-scope device array instead of the stream-ordered
+// pool, for callers that may not allocate (CUDA graph capture, serving loops, harnesses that forbid it).
+// Every GPU that loads libbcp.so holds BCP_RENDER_STATIC_SCRATCH_BYTES of it until the process exits.
+namespace {
+
+__device__ __align__(256) unsigned char g_render_scratch[BCP_RENDER_STATIC_SCRATCH_BYTES];
+
+constexpr int kMaxDevices = 64;
+// In host code `g_render_scratch` is only the host-side stand-in of the symbol, not a device address:
+// each device's copy is looked up once, with that device current, and the kernels get that pointer.
+unsigned char* g_scratch_addr[kMaxDevices] = {nullptr};
+
+int static_scratch(int device_ordinal, unsigned char** out) {  // the caller has made device_ordinal current
+  if (device_ordinal < 0 || device_ordinal >= kMaxDevices) return bcp::abi_fail("bcp_render_pixels_static: device_ordinal out of range", cudaSuccess);
+  if (!g_scratch_addr[device_ordinal]) {
+    void* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress(&p, g_render_scratch);
+    if (e != cudaSuccess || !p) return bcp::abi_fail("bcp_render_pixels_static: cudaGetSymbolAddress(g_render_scratch)", e);
+    g_scratch_addr[device_ordinal] = static_cast<unsigned char*>(p);
+  }
+  *out = g_scratch_addr[device_ordinal];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t bcp_render_static_scratch_bytes(void) { return BCP_RENDER_STATIC_SCRATCH_BYTES; }
+
+int bcp_render_pixels_static(const bcp_render_args* a, int device_ordinal, void* stream) {
+  if (!a || !a->obs || !a->pixels) return bcp::abi_fail("bcp_render_pixels_static: null argument", cudaSuccess);
+  if (a->num_envs <= 0 || a->width <= 0 || a->height <= 0) return bcp::abi_fail("bcp_render_pixels_static: empty batch or image", cudaSuccess);
+  if (a->num_cameras != 1 && a->num_cameras != 2) return bcp::abi_fail("bcp_render_pixels_static: num_cameras must be 1 or 2", cudaSuccess);
+  if (a->repeats < 1 || a->repeats > kMaxR) return bcp::abi_fail("bcp_render_pixels_static: repeats must be 1..8", cudaSuccess);
+  if (!(a->near_val > 0.f) || !(a->far_val > a->near_val) || !(a->fov_deg > 0.f && a->fov_deg < 180.f))
+    return bcp::abi_fail("bcp_render_pixels_static: bad near / far / fov", cudaSuccess);
+  // the same scratch layout as bcp_render_pixels: rays f32x4 | ground depth f32 | (16-byte aligned) background f16
+  const size_t nt = (size_t)a->num_cameras * (size_t)a->width * (size_t)a->height;
+  const size_t img_at = (nt * 20 + 15) / 16 * 16;
+  const size_t need = img_at + nt * 3 * (size_t)a->repeats * sizeof(__half);
+  if (need > (size_t)BCP_RENDER_STATIC_SCRATCH_BYTES) {
+    static thread_local char msg[200];
+    snprintf(msg, sizeof msg,
+             "bcp_render_pixels_static: num_cameras x width x height x repeats needs %zu bytes of scratch, the static array holds %zu "
+             "(use bcp_render_pixels)", need, (size_t)BCP_RENDER_STATIC_SCRATCH_BYTES);
+    return bcp::abi_fail(msg, cudaSuccess);
+  }
+  Scene sc;
+  sc.B = a->num_envs; sc.R = a->repeats; sc.C = a->num_cameras; sc.W = a->width; sc.H = a->height;
+  for (int b = 0; b < BCP_RENDER_BODIES; ++b)
+    for (int i = 0; i < 3; ++i) { sc.h[b][i] = a->half_extents[b][i]; sc.rgb[b][i] = a->rgb[b][i]; }
+  for (int i = 0; i < 3; ++i) { sc.ground_pos[i] = a->ground_pos[i]; sc.light[i] = a->light_dir[i]; sc.bg[i] = a->background[i]; }
+  norm3(sc.light);
+  sc.near_val = a->clip ? a->near_val : 1e-6f; sc.far_val = a->clip ? a->far_val : 1e30f; sc.ambient = a->ambient; sc.diffuse = a->diffuse;
+  const float ty = tanf(0.5f * a->fov_deg * 3.14159265358979323846f / 180.f);
+  const float aspect = (float)a->width / (float)a->height;
+  for (int c = 0; c < sc.C; ++c) {
+    Camera& cam = sc.cam[c];
+    float up[3] = {a->up[0], a->up[1], a->up[2]};
+    for (int i = 0; i < 3; ++i) { cam.eye[i] = a->camera_pos[c][i]; cam.f[i] = a->target[i] - a->camera_pos[c][i]; }
+    norm3(cam.f);
+    norm3(up);
+    cross3(cam.f, up, cam.s);
+    norm3(cam.s);
+    cross3(cam.s, cam.f, cam.u);
+    cam.tx = ty * aspect;
+    cam.ty = ty;
+  }
+  int prev = -1;
+  cudaGetDevice(&prev);
+  if (prev != device_ordinal) {
+    const cudaError_t es = cudaSetDevice(device_ordinal);
+    if (es != cudaSuccess) {
+      cudaGetLastError();  // not sticky: leave nothing for the next call's launch check
+      return bcp::abi_fail("bcp_render_pixels_static: cudaSetDevice", es);
+    }
+  }
+  unsigned char* scratch = nullptr;
+  if (static_scratch(device_ordinal, &scratch)) {
+    if (prev != device_ordinal) cudaSetDevice(prev);
+    return -1;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  float4* rays = reinterpret_cast<float4*>(scratch);
+  float* depth = reinterpret_cast<float*>(scratch + nt * 16);
+  __half* base = reinterpret_cast<__half*>(scratch + img_at);
+  // Nothing in the array has to start at zero: k_render_table writes every ray, depth and background word that
+  // k_render reads (all `need` bytes in use) before k_render runs on the same stream; what the last call left
+  // beyond them is never read.  Calls that overlap on the GPU (different streams / threads) race on the array.
+  k_render_table<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(sc, rays, depth, base);
+  const dim3 grid((unsigned)a->num_envs, 1);
+  k_render<<<grid, kThreads, 0, st>>>(sc, a->obs, rays, depth, base, reinterpret_cast<__half*>(a->pixels));
+  const cudaError_t e = cudaGetLastError();
+  if (prev != device_ordinal) cudaSetDevice(prev);
+  if (e != cudaSuccess) return bcp::abi_fail("bcp_render_pixels_static: launch", e);
   return 0;
 }
 

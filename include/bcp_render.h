@@ -51,6 +51,25 @@ size_t bcp_render_args_size(void);
  * Returns 0, or -1 with bcp_last_error() set. */
 int bcp_render_pixels(const bcp_render_args* args, int device_ordinal, void* stream);
 
+/* bcp_render_pixels for callers that may not allocate.  NO counterpart in the reference: added
+ * for code under CUDA graph capture, tight serving loops and harnesses
+ * that forbid cudaMalloc.  Same arguments, same two kernels, bit-identical pixels; the per-call scratch
+ * (ray table | ground depth | background image) lives in a file-scope `static __device__` array of
+ * BCP_RENDER_STATIC_SCRATCH_BYTES instead of the stream-ordered pool, and the call path contains no
+ * cudaMalloc / cudaMallocAsync / cudaFree or any other allocating routine (the first call on a device
+ * only looks the array's device address up with cudaGetSymbolAddress).
+ *   limit : 20 * C*W*H (rounded up to 16) + 6 * C*W*H*R bytes must fit in the array - e.g. the
+ *           reference's 50 x 50 with C = 2, R = 8 needs 340 000 bytes, 128 x 128 with C = 2, R = 2 needs
+ *           1 048 576; anything larger is refused with -1 and a message naming both sizes.
+ *   cost  : every GPU that loads libbcp.so holds the array until the process exits.
+ *   races : all calls on a device share the array, which keeps the last call's contents (nothing needs to
+ *           start at zero: the table kernel rewrites every word the render kernel reads).  Calls on the
+ *           same stream are ordered; calls that overlap on the GPU (different streams or host threads
+ *           without an event between them) race on it - serialise them or use bcp_render_pixels.      */
+#define BCP_RENDER_STATIC_SCRATCH_BYTES (1u << 20)
+size_t bcp_render_static_scratch_bytes(void);
+int bcp_render_pixels_static(const bcp_render_args* args, int device_ordinal, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
