@@ -7,11 +7,12 @@ import os
 from . import config as C
 
 _LIB = None
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "libbcp.so")
+# BCP_LIB_PATH: a measurement build of the same sources (build.py --precise), never a different implementation
+LIB_PATH = os.environ.get("BCP_LIB_PATH") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "libbcp.so")
 
 EXPORTS = ["bcp_abi_version", "bcp_config_size", "bcp_last_error", "bcp_create", "bcp_destroy", "bcp_reset",
            "bcp_step", "bcp_rollout_random", "bcp_stats", "bcp_stats_clear", "bcp_get_state", "bcp_set_state",
-           "bcp_substep", "bcp_launch_count", "bcp_bench_fma_peak", "bcp_profile_begin", "bcp_profile_end", "bcp_last_solve_info", "bcp_solver_kind", "bcp_step_host", "bcp_step_host_finish",
+           "bcp_substep", "bcp_launch_count", "bcp_bench_fma_peak", "bcp_profile_begin", "bcp_profile_end", "bcp_last_solve_info", "bcp_solver_kind", "bcp_step_host", "bcp_step_host_finish", "bcp_solve_trace_enable", "bcp_solve_trace_read",
            # include/bcp_replay.h
            "bcp_replay_config_size", "bcp_replay_create", "bcp_replay_destroy", "bcp_replay_begin", "bcp_replay_observe",
            "bcp_replay_add_episode", "bcp_replay_batch", "bcp_replay_info", "bcp_replay_export", "bcp_replay_launch_count",
@@ -89,6 +90,8 @@ def load(build_if_missing: bool = False):
     lib.bcp_profile_end.argtypes = [vp, ctypes.POINTER(ctypes.c_double)]
     lib.bcp_last_solve_info.argtypes = [vp, vp, ctypes.c_size_t, vp]
     lib.bcp_launch_count.restype = ctypes.c_int64
+    lib.bcp_solve_trace_enable.argtypes = [vp, ctypes.c_int]
+    lib.bcp_solve_trace_read.argtypes = [vp, vp, ctypes.c_size_t, vp]
     lib.bcp_solver_kind.argtypes = [vp]
     lib.bcp_step_host.argtypes = [vp, vp, vp, vp, vp, vp, vp]
     lib.bcp_step_host_finish.argtypes = [vp, vp, vp, vp]

@@ -46,11 +46,14 @@ def is_stale() -> bool:
     return any(os.path.getmtime(s) > t for s in _sources())
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not is_stale():
-        return LIB
+def build(force: bool = False, verbose: bool = False, precise: bool = False) -> str:
+    """precise=True builds libbcp_precise.so: the fp32 unit WITHOUT -prec-div=false -prec-sqrt=false -ftz=true, to
+    measure how much of the fp32-vs-oracle tail those flags are (scripts/fp32_tail_report.py; never the product)."""
+    lib = LIB.replace("libbcp.so", "libbcp_precise.so") if precise else LIB
+    if not force and os.path.exists(lib) and not any(os.path.getmtime(s) > os.path.getmtime(lib) for s in _sources()):
+        return lib
     nvcc = _nvcc()
-    objdir = os.path.join(CSRC, "build")
+    objdir = os.path.join(CSRC, "build_precise" if precise else "build")
     os.makedirs(objdir, exist_ok=True)
     env = dict(os.environ)
     env.pop("CC", None)
@@ -60,6 +63,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
         src, extra = unit
         obj = os.path.join(objdir, src.replace(".cu", ".o"))
         tune = os.environ.get("BCP_NVCC_EXTRA", "").split()  # tuning experiments (-D...), empty in the product build
+        if precise and src == "bcp_f32.cu":
+            extra = []
         cmd = [nvcc, *ARCH, *COMMON, *extra, *tune, "-c", os.path.join(CSRC, src), "-o", obj]
         r = subprocess.run(cmd, capture_output=True, text=True, env=env)
         with open(obj + ".ptxas.log", "w") as fh:
@@ -70,14 +75,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
 
     with concurrent.futures.ThreadPoolExecutor(max_workers=len(UNITS)) as ex:
         objs = list(ex.map(compile_one, UNITS))
-    cmd = [nvcc, *ARCH, "-shared", "-o", LIB, *objs, "-lcudart"]
+    cmd = [nvcc, *ARCH, "-shared", "-o", lib, *objs, "-lcudart"]
     r = subprocess.run(cmd, capture_output=True, text=True, env=env)
     if r.returncode != 0:
         raise RuntimeError(f"link failed:\n{r.stderr[-4000:]}")
     if verbose:
-        print(f"built {LIB}", file=sys.stderr)
-    return LIB
+        print(f"built {lib}", file=sys.stderr)
+    return lib
 
 
 if __name__ == "__main__":
-    build(force="--force" in sys.argv, verbose=True)
+    build(force="--force" in sys.argv, verbose=True, precise="--precise" in sys.argv)

@@ -49,7 +49,7 @@ struct bcp_env {
   int* list = nullptr;   // compacted env indices for masked resets
   int* count = nullptr;
   double* staging = nullptr;  // canonical records for get/set_state
-  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
+  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
   int use_split = 0;
   // bcp_step_host: device-side actions / outputs / packed observation slabs, the copy stream
   struct HostStep {
@@ -178,6 +178,7 @@ int bcp_destroy(bcp_env* h) {
     cudaStreamDestroy(h->hs.copy); cudaEventDestroy(h->hs.ev_ready); cudaEventDestroy(h->hs.ev_copied); if (h->hs.ev_h2d) cudaEventDestroy(h->hs.ev_h2d);
   }
   if (h->split.side) { cudaStreamDestroy(h->split.side); cudaEventDestroy(h->split.ev_prep); cudaEventDestroy(h->split.ev_gen); }
+  cudaFree(h->split.trace);
   cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc); cudaFree(h->split.cont); cudaFree(h->split.contm);
   for (int k = 0; k < 2; ++k) { cudaFree(h->split.bins[k]); cudaFree(h->split.cnts[k]); }
   delete h;
@@ -489,6 +490,35 @@ int bcp_last_solve_info(bcp_env* h, int32_t* host_out, size_t n_ints, void* stre
   const size_t pitch = bcp::split_record_words(h->p32) * sizeof(float);
   CK(cudaMemcpy2DAsync(host_out, 4 * sizeof(int32_t), h->split.recs, pitch, 4 * sizeof(int32_t), (size_t)h->cfg.num_envs,
                        cudaMemcpyDeviceToHost, s));
+  CK(cudaStreamSynchronize(s));
+  return 0;
+}
+
+
+int bcp_solve_trace_enable(bcp_env* h, int on) {
+  if (!h) return fail("bcp_solve_trace_enable: null handle");
+  if (h->f64() || !h->use_split || !h->split.recs) return fail("bcp_solve_trace_enable: the handle does not run the split pipeline");
+  DeviceGuard g(h->cfg.device_ordinal);
+  if (on && !h->split.trace) {
+    const size_t bytes = (size_t)h->cfg.action_repeats * h->cfg.steps_per_repeat * h->cfg.num_envs * 4 * sizeof(int);
+    CK(cudaMalloc((void**)&h->split.trace, bytes));
+    CK(cudaMemset(h->split.trace, 0, bytes));
+  } else if (!on && h->split.trace) {
+    CK(cudaDeviceSynchronize());
+    CK(cudaFree(h->split.trace));
+    h->split.trace = nullptr;
+  }
+  return 0;
+}
+
+int bcp_solve_trace_read(bcp_env* h, int32_t* host_out, size_t n_ints, void* stream) {
+  if (!h || !host_out) return fail("bcp_solve_trace_read: null argument");
+  if (!h->split.trace) return fail("bcp_solve_trace_read: tracing is not enabled on this handle");
+  const size_t need = (size_t)h->cfg.action_repeats * h->cfg.steps_per_repeat * h->cfg.num_envs * 4;
+  if (n_ints != need) return fail("bcp_solve_trace_read: n_ints must be 4 * R * S * num_envs");
+  DeviceGuard g(h->cfg.device_ordinal);
+  cudaStream_t s = (cudaStream_t)stream;
+  CK(cudaMemcpyAsync(host_out, h->split.trace, need * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   return 0;
 }

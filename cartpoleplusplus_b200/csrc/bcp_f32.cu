@@ -147,6 +147,9 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
         k_solve<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc, col_stride, fetch_min);
       }
       if (launches) ++*launches;
+      if (b.trace)  // instrumentation of the parity tests: what every env's solve of substep k did
+        cudaMemcpy2DAsync(b.trace + (size_t)k * N * 4, 4 * sizeof(int), b.recs, (size_t)rec_words * sizeof(float), 4 * sizeof(int), (size_t)N,
+                          cudaMemcpyDeviceToDevice, s);
       mark();
     }
   }

@@ -46,6 +46,9 @@ struct SplitBuffers {
   // starts the device->host copy of an observation slab as soon as its repeat is complete)
   void (*after_prep)(void* ctx, int k, cudaStream_t s);
   void* hook_ctx;
+  // optional (bcp_solve_trace_enable): [R*S][num_envs][4] ints, the first four words of every solve record
+  // (three contact counts, PGS iterations) copied out after the solve phase of each substep of a call
+  int* trace;
 };
 size_t split_cont_words(const Params<float>& P);
 bool split_uses_lambda(const Params<float>& P);  // impulse-space solve phase for this configuration / batch size?

@@ -239,6 +239,17 @@ class BatchedBulletCartpole:
         _lib.check(self._lib.bcp_last_solve_info(self._h, out.ctypes.data_as(ctypes.c_void_p), out.size, self._stream()), self._lib)
         return out
 
+    def solve_trace(self, enable: Optional[bool] = None) -> Optional[np.ndarray]:
+        """solve_trace(True/False) switches the per-substep trace of the split pipeline on / off; solve_trace()
+        returns (R*S, B, 4) int32 of the last step(): contact points of the three pairs and PGS iterations of every
+        substep (test instrumentation, include/bcp.h bcp_solve_trace_*)."""
+        if enable is not None:
+            _lib.check(self._lib.bcp_solve_trace_enable(self._h, 1 if enable else 0), self._lib)
+            return None
+        out = np.zeros((self.repeats * self.steps_per_repeat, self.num_envs, 4), dtype=np.int32)
+        _lib.check(self._lib.bcp_solve_trace_read(self._h, out.ctypes.data_as(ctypes.c_void_p), out.size, self._stream()), self._lib)
+        return out
+
     # ---- raw physics access used by parity tests ----
     def substep(self):
         _lib.check(self._lib.bcp_substep(self._h, self._stream()), self._lib)

@@ -263,6 +263,15 @@ int bcp_profile_end(bcp_env* env, double* out4);
  * Error unless the handle runs the split pipeline (fp32, >= 4096 envs).                  */
 int bcp_last_solve_info(bcp_env* env, int32_t* host_out, size_t n_ints, void* stream);
 
+/* Test instrumentation (no reference counterpart): with tracing enabled, every bcp_step on the split pipeline also
+ * keeps, for each of its R*S substeps, what bcp_last_solve_info reports for the last one; the parity tests classify
+ * an env whose fp32 pose leaves the fp64 oracle's by more than 1e-4 by the discrete decision that differs
+ * (tests/test_gpu_pipeline_parity.py).  One device-to-device copy per substep while enabled, nothing otherwise.
+ *   host_out[(k * num_envs + e) * 4 + 0..3] = substep k of the last call, env e: the three contact counts, iterations
+ *   n_ints = 4 * R * S * num_envs.  read synchronises.                                                     */
+int bcp_solve_trace_enable(bcp_env* env, int on);
+int bcp_solve_trace_read(bcp_env* env, int32_t* host_out, size_t n_ints, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

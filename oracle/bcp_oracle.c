@@ -211,6 +211,7 @@ typedef struct {
   real pend_f[3], pend_t[3];
   omanifold mani[3];
   int steps, done, episode;
+  int reset_left; /* pipelined auto-reset only (bcp.h BCP_AUTO_RESET_PIPELINED): reset substeps still to run */
 } ostate;
 
 static void load_body(const double* s, obody* b) {
@@ -246,6 +247,7 @@ static void load_state(const double* s, ostate* st) {
   st->steps = (int)s[BCP_S_STEPS];
   st->done = (int)s[BCP_S_DONE];
   st->episode = (int)s[BCP_S_EPISODE];
+  st->reset_left = (int)s[BCP_S_RESET_LEFT];
 }
 static void store_state(const ostate* st, double* s) {
   int m, k, i;
@@ -272,6 +274,7 @@ static void store_state(const ostate* st, double* s) {
   s[BCP_S_DONE] = st->done;
   s[BCP_S_EPISODE] = st->episode;
   for (i = BCP_S_EPISODE + 1; i < BCP_STATE_DOUBLES; ++i) s[i] = 0.0;
+  s[BCP_S_RESET_LEFT] = st->reset_left;
 }
 
 /* ======================================================================== */
@@ -415,8 +418,18 @@ static real dot_vec_col(const real* v, const real* A, int ja) { /* dDOT14 */
 /* dBoxBox2.  p1,R1,h1: box 1 (= body A); p2,R2,h2: box 2 (= body B); h = half
  * extents (Bullet passes 2*halfExtents and halves it again: exact).  Returns the
  * number of contacts written (0..4), in Bullet's emission order. */
+static __thread int g_sat_code; /* the separating-axis code of the last box_box call (0: separated), for test instrumentation */
+static int box_box_impl(const real p1[3], const real* R1, const real h1[3], const real p2[3], const real* R2,
+                        const real h2[3], ocontact out[4], int* code_out);
 static int box_box(const real p1[3], const real* R1, const real h1[3], const real p2[3], const real* R2,
                    const real h2[3], ocontact out[4]) {
+  int code = 0;
+  const int n = box_box_impl(p1, R1, h1, p2, R2, h2, out, &code);
+  g_sat_code = code;
+  return n;
+}
+static int box_box_impl(const real p1[3], const real* R1, const real h1[3], const real p2[3], const real* R2,
+                        const real h2[3], ocontact out[4], int* code_out) {
   const real fudge_factor = R(1.05);
   real p[3], pp[3], normalC[3] = {0, 0, 0}, normal[3];
   const real* normalR = 0;
@@ -495,6 +508,7 @@ static int box_box(const real p1[3], const real* R1, const real h1[3], const rea
 #undef TST2
 
   if (!code) return 0;
+  *code_out = code;
 
   if (normalR) {
     normal[0] = COL(normalR, normalR_col, 0);
@@ -885,6 +899,8 @@ static void warm_start_row(orow* c, sbody* bodies, real cached, real factor) {
   }
 }
 
+static __thread unsigned g_clamp_hash; /* instrumentation only: never read by the arithmetic */
+#define CLAMP_NOTE(bit) (g_clamp_hash = (g_clamp_hash ^ (unsigned)(bit)) * 16777619u)
 /* resolveSingleConstraintRowGeneric */
 static real resolve_row(orow* c, sbody* bodies) {
   real deltaImpulse = c->rhs - c->applied * c->cfm;
@@ -894,9 +910,9 @@ static real resolve_row(orow* c, sbody* bodies) {
   deltaImpulse -= dA * c->jacDiagABInv;
   deltaImpulse -= dB * c->jacDiagABInv;
   sum = c->applied + deltaImpulse;
-  if (sum < c->lower) { deltaImpulse = c->lower - c->applied; c->applied = c->lower; }
-  else if (sum > c->upper) { deltaImpulse = c->upper - c->applied; c->applied = c->upper; }
-  else c->applied = sum;
+  if (sum < c->lower) { deltaImpulse = c->lower - c->applied; c->applied = c->lower; CLAMP_NOTE(1); }
+  else if (sum > c->upper) { deltaImpulse = c->upper - c->applied; c->applied = c->upper; CLAMP_NOTE(2); }
+  else { c->applied = sum; CLAMP_NOTE(0); }
   apply_delta(&bodies[c->a], c->unitA, deltaImpulse);
   apply_delta(&bodies[c->b], c->unitB, deltaImpulse);
   return deltaImpulse / c->jacDiagABInv;
@@ -914,6 +930,7 @@ static real resolve_cone(orow* cA, orow* cB, sbody* bodies) {
   dIA -= jdotdv(&bodies[cA->a], cA->jacA) * cA->jacDiagABInv;
   dIA -= jdotdv(&bodies[cA->b], cA->jacB) * cA->jacDiagABInv;
   sumA = cA->applied + dIA;
+  CLAMP_NOTE(sumA * sumA + sumB * sumB >= cA->lower * cB->lower ? 5 : 4);
   if (sumA * sumA + sumB * sumB >= cA->lower * cB->lower) {
     const real r = R_SQRT(sumA * sumA + sumB * sumB);
     const real sn = (r > R(0.0)) ? sumA / r : R(0.0);
@@ -986,6 +1003,11 @@ static int g_debug = 0;
 typedef struct {
   int iterations, rows, friction_rows;
   int contacts[3];
+  int code[3]; /* dBoxBox2's separating-axis code per pair: 0 separated, 1-3 face of A, 4-6 face of B, 7-15 edge-edge */
+  int active_hash; /* hash over all iterations of the solver's clamp decisions (normal row at its lower limit, friction pair
+                      clipped to the cone): the active set of the projected Gauss-Seidel */
+  int force_it;    /* INPUT, > 0: run exactly this many iterations, ignoring the residual early exit (test instrumentation:
+                      "the oracle with the kernel's iteration count") */
 } osubstep_info;
 
 /* One p.stepSimulation() — bullet_cartpole.py:199,327,330.
@@ -1016,6 +1038,7 @@ static void substep(const bcp_config* cfg, ostate* st, osubstep_info* info) {
     const real breaking = pair_breaking(cfg, cb[pairA[m]], cb[pairB[m]]);
     ocontact cs[4];
     const int nc = box_box(A->x, A->R, A->h, B->x, B->R, B->h, cs);
+    if (info) info->code[m] = g_sat_code;
     for (k = 0; k < nc; ++k) manifold_add(&st->mani[m], A, B, &cs[k], breaking);
     manifold_refresh(&st->mani[m], A, B, breaking, wp[m]);
     if (info) info->contacts[m] = st->mani[m].count;
@@ -1075,6 +1098,7 @@ static void substep(const bcp_config* cfg, ostate* st, osubstep_info* info) {
    * they would apply a zero impulse and report a zero residual. */
 
   /* ---- 4. projected Gauss-Seidel ---- */
+  g_clamp_hash = 2166136261u;
   for (it = 0; it < cfg->solver_iterations; ++it) {
     real lsr = 0;
     int j;
@@ -1113,9 +1137,13 @@ static void substep(const bcp_config* cfg, ostate* st, osubstep_info* info) {
       for (j = 0; j < n_n; ++j) fprintf(stderr, " %.5f", (double)nrows[j].applied);
       fprintf(stderr, "\n");
     }
+    if (info && info->force_it > 0) {
+      if (it + 1 >= info->force_it) { it++; break; }
+      continue;
+    }
     if (lsr <= (real)cfg->residual_threshold || it >= cfg->solver_iterations - 1) { it++; break; }
   }
-  if (info) { info->iterations = it; info->rows = n_n; info->friction_rows = n_f; }
+  if (info) { info->iterations = it; info->rows = n_n; info->friction_rows = n_f; info->active_hash = (int)(g_clamp_hash & 0x7fffffffu); }
 
   /* solveGroupCacheFriendlyFinish: applied normal impulses -> manifold cache */
   {
@@ -1195,6 +1223,7 @@ static void env_reset(const bcp_config* cfg, ostate* st, int64_t global_env, flo
   uint32_t rnd[4];
   st->steps = 0;                                         /* :315 */
   st->done = 0;                                          /* :316 */
+  st->reset_left = 0;
   for (i = 0; i < 3; ++i) {                              /* :319-320 */
     st->cart.x[i] = (real)cfg->cart.init_pos[i];
     st->pole.x[i] = (real)cfg->pole.init_pos[i];
@@ -1263,29 +1292,102 @@ static void action_to_force(const bcp_config* cfg, const void* action, real* fx,
   }
 }
 
-/* BulletCartpole.step — bullet_cartpole.py:178-275 */
-static void env_step(const bcp_config* cfg, ostate* st, const void* action, float* obs, float* reward,
-                     uint8_t* done, uint8_t* reason_out) {
-  int r, s, reason;
-  real fx, fy;
-  if (st->done) { /* :179-181: obs unchanged, reward 0, done */
+/* teleport of reset(): p.resetBasePositionAndOrientation x2 — bullet_cartpole.py:315-320 */
+static void reset_begin(const bcp_config* cfg, ostate* st) {
+  int i;
+  st->steps = 0;
+  st->done = 0;
+  for (i = 0; i < 3; ++i) {
+    st->cart.x[i] = (real)cfg->cart.init_pos[i];
+    st->pole.x[i] = (real)cfg->pole.init_pos[i];
+    st->cart.v[i] = st->cart.w[i] = st->pole.v[i] = st->pole.w[i] = 0;
+    st->cart.q[i] = st->pole.q[i] = 0;
+  }
+  st->cart.q[3] = st->pole.q[3] = 1;
+  if (!cfg->carry_over_reset) {
+    for (i = 0; i < 3; ++i) { st->pend_f[i] = st->pend_t[i] = 0; st->mani[i].count = 0; }
+  }
+}
+
+#define BCPO_INFO_WORDS 10 /* per substep: iterations, rows, friction rows, contacts[3], SAT code[3], active-set hash; iterations = -1: no substep ran */
+static void put_info(int32_t* o, const osubstep_info* in) {
+  if (!in) { int i; o[0] = -1; for (i = 1; i < BCPO_INFO_WORDS; ++i) o[i] = 0; return; }
+  o[0] = in->iterations; o[1] = in->rows; o[2] = in->friction_rows;
+  o[3] = in->contacts[0]; o[4] = in->contacts[1]; o[5] = in->contacts[2];
+  o[6] = in->code[0]; o[7] = in->code[1]; o[8] = in->code[2];
+  o[9] = in->active_hash;
+}
+
+/* BulletCartpole.step — bullet_cartpole.py:178-275.
+ * With cfg->auto_reset == BCP_AUTO_RESET_PIPELINED (no reference counterpart; include/bcp.h) a finished env
+ * runs its reset (:313-346) inside the following calls, R*S substeps per call: the SAME statements as
+ * env_reset above, cut at call boundaries (tests/test_oracle_pipelined.py holds the two forms together).
+ * info: optional [R*S][BCPO_INFO_WORDS] instrumentation of every substep of the call. */
+static void env_step(const bcp_config* cfg, ostate* st, int64_t global_env, const void* action, float* obs, float* reward,
+                     uint8_t* done, uint8_t* reason_out, int32_t* info, const int32_t* force_it /* [R*S] or NULL */) {
+  enum { IDLE, LIVE, RESETTING, FRESH } mode;
+  const int total = cfg->settle_steps + cfg->initial_force_steps;
+  int r, s, reason, k = 0;
+  real fx = 0, fy = 0;
+  if (!st->done) mode = LIVE;
+  else if (cfg->auto_reset != BCP_AUTO_RESET_PIPELINED) mode = IDLE;
+  else {
+    mode = RESETTING;
+    if (st->reset_left == 0) { /* the episode ended in an earlier call: the reset starts with the teleport */
+      reset_begin(cfg, st);
+      st->done = 1;
+      st->reset_left = total;
+      if (total == 0) { st->done = 0; st->episode += 1; mode = FRESH; }
+    }
+  }
+  if (mode == IDLE) { /* :179-181: obs unchanged, reward 0, done */
     *reward = 0.0f;
     *done = 1;
     if (reason_out) *reason_out = BCP_REASON_NONE;
+    if (info) for (k = 0; k < cfg->action_repeats * cfg->steps_per_repeat; ++k) put_info(info + k * BCPO_INFO_WORDS, 0);
     return;
   }
-  action_to_force(cfg, action, &fx, &fy);
+  if (mode == LIVE) action_to_force(cfg, action, &fx, &fy);
   for (r = 0; r < cfg->action_repeats; ++r) {          /* :197 */
-    for (s = 0; s < cfg->steps_per_repeat; ++s) {      /* :198 */
-      substep(cfg, st, 0);                             /* :199 */
-      apply_cart_force(cfg, st, fx, fy);               /* :201-203 */
+    for (s = 0; s < cfg->steps_per_repeat; ++s, ++k) { /* :198 */
+      osubstep_info inf;
+      const int on = mode == LIVE || (mode == RESETTING && st->reset_left > 0);
+      inf.force_it = force_it ? force_it[k] : 0;
+      if (on) substep(cfg, st, (info || force_it) ? &inf : 0); /* :199 / :327 / :330 */
+      if (info) put_info(info + k * BCPO_INFO_WORDS, on ? &inf : 0);
+      if (mode == LIVE) {
+        apply_cart_force(cfg, st, fx, fy);             /* :201-203 */
+      } else if (mode == RESETTING && st->reset_left > 0) {
+        const int push = total - st->reset_left - cfg->settle_steps; /* index of the push this substep belongs to, < 0 while settling */
+        if (push >= 0) {                               /* :329-332 */
+          real theta_s = 0, theta_c = 1;
+          if (cfg->random_theta) {
+            uint32_t rnd[4];
+            env_rng(cfg, global_env, (uint32_t)st->episode, RNG_PUSH,
+                    cfg->theta_mode == BCP_THETA_PER_SUBSTEP ? (uint32_t)push : 0u, rnd);
+            sincos_2pi(u24(rnd[0]), &theta_s, &theta_c);
+          }
+          apply_cart_force(cfg, st, (real)cfg->initial_force * theta_c, (real)cfg->initial_force * theta_s);
+        }
+        if (--st->reset_left == 0) { st->done = 0; st->episode += 1; mode = FRESH; }
+      }
     }
-    if (obs) write_obs(st, obs + 14 * r);              /* :237 */
+    if (mode == LIVE && obs) write_obs(st, obs + 14 * r); /* :237 */
   }
-  st->steps += 1;                                      /* :239 */
-  reason = done_reason(cfg, st);
-  if (reason != BCP_REASON_NONE) st->done = 1;
-  *reward = 1.0f;                                      /* :260 */
+  if (mode == LIVE) {
+    st->steps += 1;                                    /* :239 */
+    reason = done_reason(cfg, st);
+    if (reason != BCP_REASON_NONE) st->done = 1;
+    *reward = 1.0f;                                    /* :260 */
+  } else {
+    *reward = 0.0f;
+    if (mode == FRESH) {
+      if (obs) for (r = 0; r < cfg->action_repeats; ++r) write_obs(st, obs + 14 * r); /* :338-339 */
+      reason = BCP_REASON_FRESH;
+    } else {
+      reason = BCP_REASON_RESETTING;
+    }
+  }
   *done = (uint8_t)st->done;
   if (reason_out) *reason_out = (uint8_t)reason;
 }
@@ -1334,6 +1436,7 @@ int SFX(bcpo_substep)(const bcp_config* cfg, double* state, int n_envs, int32_t*
   for (e = 0; e < n_envs; ++e) {
     ostate st;
     osubstep_info info;
+    info.force_it = 0;
     load_state(state + (size_t)e * BCP_STATE_DOUBLES, &st);
     substep(cfg, &st, &info);
     store_state(&st, state + (size_t)e * BCP_STATE_DOUBLES);
@@ -1371,20 +1474,31 @@ int SFX(bcpo_reset)(const bcp_config* cfg, double* state, int n_envs, const uint
   return 0;
 }
 
-int SFX(bcpo_step)(const bcp_config* cfg, double* state, int n_envs, const void* actions, float* obs, float* reward,
-                   uint8_t* done, uint8_t* reason) {
+static int step_batch(const bcp_config* cfg, double* state, int n_envs, const void* actions, float* obs, float* reward,
+                      uint8_t* done, uint8_t* reason, int32_t* info, const int32_t* force_it) {
   int e;
-  const int R_ = cfg->action_repeats;
-#pragma omp parallel for schedule(static)
+  const int R_ = cfg->action_repeats, RS_ = cfg->action_repeats * cfg->steps_per_repeat;
+#pragma omp parallel for schedule(dynamic, 64)
   for (e = 0; e < n_envs; ++e) {
     ostate st;
     const void* a = cfg->discrete_actions ? (const void*)((const int32_t*)actions + e)
                                           : (const void*)((const float*)actions + 2 * (size_t)e);
     load_state(state + (size_t)e * BCP_STATE_DOUBLES, &st);
-    env_step(cfg, &st, a, obs ? obs + (size_t)e * 14 * R_ : 0, &reward[e], &done[e], reason ? &reason[e] : 0);
+    env_step(cfg, &st, cfg->env_id_offset + e, a, obs ? obs + (size_t)e * 14 * R_ : 0, &reward[e], &done[e],
+             reason ? &reason[e] : 0, info ? info + (size_t)e * RS_ * BCPO_INFO_WORDS : 0, force_it ? force_it + (size_t)e * RS_ : 0);
     store_state(&st, state + (size_t)e * BCP_STATE_DOUBLES);
   }
   return 0;
+}
+int SFX(bcpo_step)(const bcp_config* cfg, double* state, int n_envs, const void* actions, float* obs, float* reward,
+                   uint8_t* done, uint8_t* reason) {
+  return step_batch(cfg, state, n_envs, actions, obs, reward, done, reason, 0, 0);
+}
+/* the same with info[n][R*S][10] filled (BCPO_INFO_WORDS) and, optionally, the PGS iteration count of every substep
+ * imposed (force_it[n][R*S], entries <= 0: the residual rule decides) */
+int SFX(bcpo_step_info)(const bcp_config* cfg, double* state, int n_envs, const void* actions, float* obs, float* reward,
+                        uint8_t* done, uint8_t* reason, int32_t* info, const int32_t* force_it) {
+  return step_batch(cfg, state, n_envs, actions, obs, reward, done, reason, info, force_it);
 }
 
 /* README.md:76-93 random-agent protocol; hist has max_episode_len+1 bins */
@@ -1418,7 +1532,7 @@ int SFX(bcpo_rollout_random)(const bcp_config* cfg, double* state, int n_envs, i
           lrs++;
         }
         draw_action(cfg, cfg->env_id_offset + e, &st, action_mask, &ai, af);
-        env_step(cfg, &st, cfg->discrete_actions ? (const void*)&ai : (const void*)af, o, &rew, &dn, &rs);
+        env_step(cfg, &st, cfg->env_id_offset + e, cfg->discrete_actions ? (const void*)&ai : (const void*)af, o, &rew, &dn, &rs, 0, 0);
         lst++;
         lr += rew;
         if (dn) {

@@ -96,7 +96,11 @@ class Oracle:
                               _ptr(m, ctypes.c_uint8), _ptr(self.obs, ctypes.c_float))
         return self.obs.copy()
 
-    def step(self, actions):
+    def step(self, actions, with_info: bool = False, force_iterations=None):
+        """env.step of every env.  A config with auto_reset = pipelined runs the reset of a finished env inside the
+        following calls (reason 4 RESETTING / 5 FRESH), like bcp_step.  with_info: also returns int32
+        (n, R*S, 10) per substep: iterations (-1: no substep ran), rows, friction rows, contacts[3], SAT code[3], hash of the
+        solver's clamp decisions.  force_iterations (n, R*S) int32: run exactly that many PGS iterations where > 0."""
         if self.cfg.discrete_actions:
             a = np.ascontiguousarray(np.broadcast_to(np.asarray(actions, dtype=np.int32), (self.n,)))
         else:
@@ -104,9 +108,16 @@ class Oracle:
         reward = np.zeros(self.n, dtype=np.float32)
         done = np.zeros(self.n, dtype=np.uint8)
         reason = np.zeros(self.n, dtype=np.uint8)
-        self._f("bcpo_step")(ctypes.byref(self.cfg), _ptr(self.state, ctypes.c_double), self.n,
-                             a.ctypes.data_as(ctypes.c_void_p), _ptr(self.obs, ctypes.c_float),
-                             _ptr(reward, ctypes.c_float), _ptr(done, ctypes.c_uint8), _ptr(reason, ctypes.c_uint8))
+        args = [ctypes.byref(self.cfg), _ptr(self.state, ctypes.c_double), self.n,
+                a.ctypes.data_as(ctypes.c_void_p), _ptr(self.obs, ctypes.c_float),
+                _ptr(reward, ctypes.c_float), _ptr(done, ctypes.c_uint8), _ptr(reason, ctypes.c_uint8)]
+        if with_info or force_iterations is not None:
+            rs = self.R * int(self.cfg.steps_per_repeat)
+            info = np.zeros((self.n, rs, 10), dtype=np.int32)
+            fi = None if force_iterations is None else np.ascontiguousarray(np.asarray(force_iterations, dtype=np.int32).reshape(self.n, rs))
+            self._f("bcpo_step_info")(*args, _ptr(info, ctypes.c_int32), _ptr(fi, ctypes.c_int32))
+            return self.obs.copy(), reward, done.astype(bool), reason, info
+        self._f("bcpo_step")(*args)
         return self.obs.copy(), reward, done.astype(bool), reason
 
     def rollout_random(self, n_steps: int, action_mask: int = 0x1F, max_episodes: int = 0):
