@@ -159,8 +159,10 @@ def _fill_body(dst: BcpBody, body: _urdf.BoxBody, init_pos, inertia_from_file: b
 
 def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dtype: Optional[str] = None,
                 seed: Optional[int] = None, device: Optional[int] = None, env_id_offset: int = 0,
-                physics: Optional[PhysicsParams] = None, scene=None) -> BcpConfig:
-    """Build the POD config from an argparse namespace (`opts.add_opts` flags)."""
+                physics: Optional[PhysicsParams] = None, scene=None, init_offset=(0.0, 0.0)) -> BcpConfig:
+    """Build the POD config from an argparse namespace (`opts.add_opts` flags).
+    init_offset: (x, y) added to the cart's and the pole's load / reset position - the fork's second cart-pole is
+    the same pair of bodies loaded at x = 1 (bullet_cartpole.py:159-160,322-323)."""
     g = lambda name, default: getattr(opts, name, default)  # noqa: E731 (reference opts lack the extras)
     if g("num_cameras", 1) not in (1, 2):
         raise ValueError("--num-cameras must be 1 or 2")  # bullet_cartpole.py:113-114
@@ -206,8 +208,9 @@ def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dt
     c.sin_angle_threshold = math.sin(ANGLE_THRESHOLD)
     c.tan_angle_threshold = math.tan(ANGLE_THRESHOLD)
     _fill_body(c.ground, ground, INIT_POS["ground"], physics.inertia_from_file)
-    _fill_body(c.cart, cart, INIT_POS["cart"], physics.inertia_from_file)
-    _fill_body(c.pole, pole, INIT_POS["pole"], physics.inertia_from_file)
+    off = (float(init_offset[0]), float(init_offset[1]), 0.0)
+    _fill_body(c.cart, cart, tuple(a + b for a, b in zip(INIT_POS["cart"], off)), physics.inertia_from_file)
+    _fill_body(c.pole, pole, tuple(a + b for a, b in zip(INIT_POS["pole"], off)), physics.inertia_from_file)
     c.dt = physics.dt
     for i in range(3):
         c.gravity[i] = physics.gravity[i]

@@ -24,7 +24,7 @@ from . import config as C
 class BatchedBulletCartpole:
     def __init__(self, opts, discrete_actions: bool, num_envs: Optional[int] = None, device=None,
                  dtype: Optional[str] = None, seed: Optional[int] = None, env_id_offset: int = 0,
-                 physics: Optional[C.PhysicsParams] = None, scene=None):
+                 physics: Optional[C.PhysicsParams] = None, scene=None, init_offset=(0.0, 0.0)):
         if not torch.cuda.is_available():
             raise _lib.BcpError("BatchedBulletCartpole needs a CUDA device: the env step has no CPU path")
         self._lib = _lib.load()
@@ -32,7 +32,8 @@ class BatchedBulletCartpole:
             device = getattr(opts, "device", 0)
         self.device = torch.device("cuda", int(device) if not isinstance(device, torch.device) else device.index or 0)
         self.cfg = C.make_config(opts, discrete_actions, num_envs=num_envs, dtype=dtype, seed=seed,
-                                 device=self.device.index, env_id_offset=env_id_offset, physics=physics, scene=scene)
+                                 device=self.device.index, env_id_offset=env_id_offset, physics=physics, scene=scene,
+                                 init_offset=init_offset)
         self.num_envs = int(self.cfg.num_envs)
         self.discrete_actions = bool(discrete_actions)
         self.repeats = int(self.cfg.action_repeats)
