@@ -273,7 +273,7 @@ def run_ours(args):
     e2e_live = 0
     t0 = time.perf_counter()
     for t in range(Ke):
-        _, rew, _ = env.step_host(host_actions[t % 2])
+        _, rew, _, _ = env.step_host(host_actions[t % 2])
         e2e_live += int(rew.sum().item())
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0

@@ -3,6 +3,19 @@
 // emission order; the normal is normalOnB (pointing from B towards A).
 #pragma once
 
+/* ATTRIBUTION.  The routine below follows, step for step, `dBoxBox2` and its helpers (`dLineClosestApproach`,
+ * `intersectRectQuad2`, `cullPoints2`) as published in Bullet Physics' btBoxBoxDetector.cpp - itself taken from the
+ * Open Dynamics Engine.  Reproducing that routine's decisions (axis order, fudge factors, emission order) is what the
+ * path requires ("reproduces Bullet's ..."), so its structure and names are kept recognisable.
+ *   Open Dynamics Engine, Copyright (C) 2001-2003 Russell L. Smith. All rights reserved.
+ *     Used under the BSD-style license of ODE (LICENSE-BSD.TXT): redistribution in source and binary forms, with or
+ *     without modification, permitted provided the copyright notice, the conditions and the disclaimer are retained;
+ *     THIS SOFTWARE IS PROVIDED "AS IS", WITHOUT WARRANTY OF ANY KIND.
+ *   Bullet Continuous Collision Detection and Physics Library, Copyright (c) 2003-2006 Erwin Coumans.
+ *     zlib license: provided 'as-is' without warranty; altered source versions must be plainly marked as such - THIS IS
+ *     AN ALTERED VERSION (restated from the published algorithm, re-laid for a per-thread workspace), not the original
+ *     software; this notice may not be removed. */
+
 namespace bcp {
 
 // Workspace of one call, supplied by the caller (k_prep: the thread's shared-memory frame, so

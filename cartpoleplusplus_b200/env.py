@@ -54,10 +54,16 @@ class BatchedBulletCartpole:
             self._renderer = PixelRenderer(self.cfg.num_envs, self.repeats, getattr(opts, "num_cameras", 1),
                                            getattr(opts, "render_width", 50), getattr(opts, "render_height", 50),
                                            scene=scene, device=self.device)
-            self.observation_space = spaces.Box(0.0, 1.0, self._renderer.state_shape)
+            self.observation_space = spaces.Box(-float_max, float_max, self._renderer.state_shape)  # :138-141, pixel mode too
         h = ctypes.c_void_p()
         _lib.check(self._lib.bcp_create(ctypes.byref(self.cfg), ctypes.byref(h)), self._lib)
         self._h = h
+        # open event log, bullet_cartpole.py:97-102: one file for the batch, an episode is written when it ends
+        self.event_log = None
+        if getattr(opts, "event_log_out", None):
+            if self.use_raw_pixels:
+                raise NotImplementedError("--event-log-out with --use-raw-pixels: the PNG render records of event.proto are not built")
+            self.event_log = self._open_event_log(opts.event_log_out)
         n, dev = self.num_envs, self.device
         # the four outputs of a call are views of ONE device buffer, so that a host-side caller
         # fetches them with a single device->host copy (step_host)
@@ -70,6 +76,10 @@ class BatchedBulletCartpole:
         self.reason = self._out[ob + rb + n:]
         self._was_reset = False
 
+    def _open_event_log(self, path):
+        from .event_log import BatchedEventLog
+        return BatchedEventLog(path, self.num_envs)
+
     # ---- gym no-ops, bullet_cartpole.py:169-176 ----
     def configure(self, display=None):
         pass
@@ -81,6 +91,9 @@ class BatchedBulletCartpole:
         pass
 
     def close(self):
+        if getattr(self, "event_log", None) is not None:
+            self.event_log.close()
+            self.event_log = None
         if getattr(self, "_h", None):
             self._lib.bcp_destroy(self._h)
             self._h = None
@@ -111,7 +124,16 @@ class BatchedBulletCartpole:
         else:
             self.done.masked_fill_(mask.bool(), 0)
         self._was_reset = True
+        if self.event_log is not None:  # :342-344: event_log.reset(); add_just_state(state)
+            self._log_reset(None if mask is None else mask.cpu().numpy())
         return self._state(copy)
+
+    def _log_reset(self, mask):
+        self.event_log.begin(self.obs.cpu().numpy(), mask)
+
+    def _log_step(self, actions):
+        a = actions.detach().cpu().numpy().reshape(self.num_envs, -1).astype(np.float32)
+        self.event_log.observe(a, self.obs.cpu().numpy(), self.reward.cpu().numpy(), self.done.cpu().numpy(), self.reason.cpu().numpy())
 
     def _state(self, copy: bool) -> torch.Tensor:
         if self._renderer is not None:
@@ -145,6 +167,8 @@ class BatchedBulletCartpole:
         _lib.check(self._lib.bcp_step(self._h, ctypes.c_void_p(a.data_ptr()), ctypes.c_void_p(self.obs.data_ptr()),
                                       ctypes.c_void_p(self.reward.data_ptr()), ctypes.c_void_p(self.done.data_ptr()),
                                       ctypes.c_void_p(self.reason.data_ptr()), self._stream()), self._lib)
+        if self.event_log is not None:  # :272-273: event_log.add(state, action, reward)
+            self._log_step(a)
         info = {"done_reason": self.reason.clone() if copy else self.reason}
         if copy:
             return self._state(True), self.reward.clone(), self.done.bool(), info
@@ -156,7 +180,10 @@ class BatchedBulletCartpole:
         obs/reward/done into pinned buffers - the observation slab of a repeat leaves as soon as that
         repeat is complete, beside the remaining substeps - one stream sync.  Returns CPU tensors
         (views of pinned buffers, overwritten by the next call): obs (B,R,2,7) as a permuted view of
-        the repeat-major buffer the copies fill, reward (B,), done (B,) uint8.
+        the repeat-major buffer the copies fill, reward (B,), done (B,) uint8, info {'done_reason': (B,) uint8} - with
+        auto_reset='pipelined' codes 4 / 5 tell reset progress and reset observations from transitions.
+        The call's outputs live in the library's own device block: the DEVICE tensors env.obs / env.reward / env.done /
+        env.reason are those of the last step() and are NOT updated by this call (use the returned host tensors).
         auto_reset=True (reset(mask=done) after the step, so that the next observation of a finished
         env is its reset observation) takes the plain path: step, one D2H, reset."""
         n, R = self.num_envs, self.repeats
@@ -180,7 +207,7 @@ class BatchedBulletCartpole:
             self._h_out.copy_(self._out, non_blocking=True)  # obs, reward, done, reason in one transfer
             self.reset(mask=self.done, copy=False)
             torch.cuda.current_stream(self.device).synchronize()
-            return self._h_obs, self._h_reward, self._h_done
+            return self._h_obs, self._h_reward, self._h_done, {"done_reason": self._h_reason}
         if not self._was_reset:
             raise _lib.BcpError("step() before reset()")
         a = actions_host
@@ -193,7 +220,10 @@ class BatchedBulletCartpole:
         _lib.check(self._lib.bcp_step_host(self._h, vp(a.data_ptr()), vp(self._h_obs_rm.data_ptr()), vp(self._h_reward.data_ptr()),
                                            vp(self._h_done.data_ptr()), vp(self._h_reason.data_ptr()), st), self._lib)
         _lib.check(self._lib.bcp_step_host_finish(self._h, vp(self._h_obs_rm.data_ptr()), vp(self._h_reason.data_ptr()), st), self._lib)
-        return self._h_obs_rm.permute(1, 0, 2, 3), self._h_reward, self._h_done
+        if self.event_log is not None:
+            self.event_log.observe(a.numpy().reshape(n, -1), self._h_obs_rm.permute(1, 0, 2, 3).numpy(), self._h_reward.numpy(), self._h_done.numpy(),
+                                   self._h_reason.numpy())
+        return self._h_obs_rm.permute(1, 0, 2, 3), self._h_reward, self._h_done, {"done_reason": self._h_reason}
 
     @property
     def h2d_bytes_per_step(self) -> int:
@@ -220,7 +250,9 @@ class BatchedBulletCartpole:
                                                 self._stream()), self._lib)
 
     def stats(self):
-        """(hist int64[max_len+1], dict(episodes, env_steps, substeps, resets), reward_sum)."""
+        """(hist int64[max_len+1], dict(episodes, env_steps, substeps, resets), reward_sum).  The histogram, episodes and
+        env_steps count every finished episode / live step of step() and rollout_random() alike; substeps, resets and
+        reward_sum are accumulated by rollout_random() only (step() returns the rewards to its caller)."""
         hist = np.zeros(self.max_episode_len + 1, dtype=np.int64)
         header = np.zeros(C.STATS_HEADER, dtype=np.int64)
         rsum = np.zeros(1, dtype=np.float64)
@@ -299,17 +331,31 @@ class BulletCartpole(BatchedBulletCartpole):
         kw["num_envs"] = 1
         super().__init__(opts, discrete_actions, **kw)
 
+    def _open_event_log(self, path):  # the reference's own writer semantics: an episode goes out at the next reset() (:48-58)
+        from .event_log import EventLog
+        return EventLog(path, self.use_raw_pixels)
+
+    def _log_reset(self, mask):
+        self.event_log.reset()
+        self.event_log.add_just_state(self.obs[0].cpu().numpy())
+
+    def _log_step(self, actions):  # :272-273 logs the caller's action object: an int, or the (1, 2) array
+        a = self._last_action
+        self.event_log.add(self.obs[0].cpu().numpy(), int(a) if self.discrete_actions else np.asarray(a, dtype=np.float32).reshape(1, 2), 1.0)
+
     def reset(self):
         return super().reset(copy=False)[0].cpu().numpy().copy()
 
     def step(self, action):
         if bool(self.done[0].item()):  # :179-181
             print("calling step after done????", file=sys.stderr)
-            return self.obs[0].cpu().numpy().copy(), 0, True, {}
+            return self._state(False)[0].cpu().numpy().copy(), 0, True, {}
         if self.discrete_actions:
             a = np.asarray(action).reshape(-1)[:1].astype(np.int64)
+            self._last_action = int(a[0])
         else:
             a = np.asarray(action, dtype=np.float32).reshape(1, 2)
+            self._last_action = a
         obs, _reward, done, info = super().step(a, copy=False)
         out = {}
         code = int(info["done_reason"][0].item())

@@ -75,11 +75,24 @@ def run_random_agent(env, num_eval: int, actions: Iterable[int] = (0, 1, 2, 3, 4
     """Run `num_eval` episodes of the random agent on `env` (a BatchedBulletCartpole): each env
     delivers ceil(num_eval / num_envs) episodes, then idles.  Returns (hist, header dict).
     Discrete envs draw uniformly from `actions`; continuous envs draw U(-1,1)^2."""
+    from . import config as C
     per_env = int(math.ceil(num_eval / env.num_envs))
+    # The kernel idles an env whose reset count has reached `max_episodes`, and that count is cumulative.  Start every env
+    # from the same count, finished: episodes that were in flight are abandoned, the RNG's episode word keeps advancing, so
+    # a second protocol run on the same env plays new episodes and delivers its full share.
+    base = 0
+    if env._was_reset:
+        st = env.get_state()
+        base = int(st[:, C.S_EPISODE].max())
+        if not ((st[:, C.S_DONE] == 1).all() and (st[:, C.S_EPISODE] == base).all() and (st[:, C.S_RESET_LEFT] == 0).all()):
+            st[:, C.S_DONE] = 1
+            st[:, C.S_EPISODE] = base
+            st[:, C.S_RESET_LEFT] = 0
+            env.set_state(st)
     env.clear_stats()
     want = per_env * env.num_envs
     for _ in range(max_launches):
-        env.rollout_random(calls_per_launch, actions=actions, max_episodes=per_env)
+        env.rollout_random(calls_per_launch, actions=actions, max_episodes=base + per_env)
         hist, header, _ = env.stats()
         if header["episodes"] >= want:
             return hist, header

@@ -66,7 +66,7 @@ import time as _t
 torch.cuda.synchronize()
 t0 = _t.perf_counter()
 for _ in range(50):
-    o, r, d = env.step_host(ha)
+    o, r, d, _ = env.step_host(ha)
     s_ = int(r.sum().item())
 t1 = _t.perf_counter()
 print("step_host (bcp_step_host) wall per step incl. reward read:", round((t1 - t0) / 50 * 1e3, 4), "ms")

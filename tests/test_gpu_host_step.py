@@ -24,11 +24,11 @@ def test_step_host_equals_step(built, n, dtype, kw):
     for t in range(90 if kw.get("auto_reset") else 12):
         act = torch.from_numpy(rng.uniform(-1, 1, size=(n, 2)).astype(np.float32))
         obs, rew, done, info = a.step(act.cuda())
-        h_obs, h_rew, h_done = b.step_host(act.pin_memory() if t % 2 else act)  # pinned and pageable callers
+        h_obs, h_rew, h_done, h_info = b.step_host(act.pin_memory() if t % 2 else act)  # pinned and pageable callers
         assert h_obs.shape == obs.shape
         assert torch.equal(h_obs, obs.cpu()), t
         assert torch.equal(h_rew, rew.cpu()) and torch.equal(h_done.bool(), done.cpu())
-        assert torch.equal(b._h_reason, info["done_reason"].cpu())
+        assert torch.equal(h_info["done_reason"], info["done_reason"].cpu())
         fresh += int((info["done_reason"] == 5).sum())
     if kw.get("auto_reset") and a.repeats > 1:
         assert fresh > 0  # the reset observations that arrive after the early slabs were exercised
