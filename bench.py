@@ -41,50 +41,40 @@ def workload_opts(args, **extra):
 
 
 # ---------------------------------------------------------------------------------------
-# flop model of the solve (FMA = 2 flops, useful work only: masked lanes,
-# padding and recomputation do not count).  One row update / one cone update of two rows.
+# Algorithmic work per unit.
+#  flops: profiles/flops_model.json - COUNTED on the parity substep (the oracle's own operation sequence) by
+#         scripts/count_flops.py: flops(substep) = fixed[gc,cp,gp] + iterations * pgs_per_iteration[gc,cp,gp], FMA = 2,
+#         useful work only.  Evaluated here on the kernel's own solve records (contact counts, iterations) - no oracle.
+#  bytes: SURVEY.md 8d - per env-step of the step-per-launch API: action in, (R,2,7) obs + reward + done + reason out, and
+#         the env's state once in and once out (26 body scalars + 6 pending force / torque + 3 x 4 x 11 manifold scalars,
+#         8 counters): what a single-launch step would have to move.
 # ---------------------------------------------------------------------------------------
-F_ROW1, F_ROW2 = 36.0, 61.0      # normal row touching one / two dynamic bodies
-F_CONE1, F_CONE2 = 83.0, 133.0   # the two friction rows of one contact, cone-clipped
+def load_flops_model(cfg):
+    path = os.path.join(ROOT, "profiles", "flops_model.json")
+    blob = json.load(open(path))
+    friction = (cfg.cart.friction * cfg.pole.friction) != 0.0
+    name = "upstream_style_friction" if friction else "configs2_fork_defaults"
+    return name, blob["workloads"][name]
 
 
-def solve_flops(info, cfg):
-    """Useful flops of the PGS solve of one substep for the envs censused in `info`
-    (oracle substep info rows: iterations, rows, friction rows, contacts gc/cp/gp)."""
-    it = info[:, 0].astype(np.float64)
-    gc, cp, gp = (info[:, 3 + k].astype(np.float64) for k in range(3))
-    mu = {"gc": cfg.ground.friction * cfg.cart.friction, "cp": cfg.cart.friction * cfg.pole.friction,
-          "gp": cfg.ground.friction * cfg.pole.friction}
-    per_iter = gc * F_ROW1 + gp * F_ROW1 + cp * F_ROW2
-    if cfg.friction_dirs == 2:
-        per_iter += (gc * F_CONE1 if mu["gc"] else 0) + (gp * F_CONE1 if mu["gp"] else 0) + (cp * F_CONE2 if mu["cp"] else 0)
-    return it * per_iter
+def substep_flops(model, counts):
+    """counts (m, 4) int: gc, cp, gp contact points and PGS iterations of m env-substeps -> (fixed flops, pgs flops) per row"""
+    fixed = np.empty(len(counts))
+    pgs = np.empty(len(counts))
+    keys, inv = np.unique(counts[:, :3], axis=0, return_inverse=True)
+    inv = inv.reshape(-1)
+    for k, key in enumerate(keys):
+        r = model["regimes"].get("%d,%d,%d" % tuple(int(v) for v in key), model["fallback"])
+        m = inv == k
+        fixed[m] = r["fixed_total"]
+        pgs[m] = r["pgs_per_iteration"] * counts[m, 3]
+    return fixed, pgs
 
 
-def _row_words(info, cfg):
-    gc, cp, gp = (info[:, 3 + k].astype(np.float64) for k in range(3))
-    rpc = lambda a, b: 3 if (a * b) and cfg.friction_dirs == 2 else 1  # noqa: E731
-    return (gc * rpc(cfg.ground.friction, cfg.cart.friction) * 8 + gp * rpc(cfg.ground.friction, cfg.pole.friction) * 8
-            + cp * rpc(cfg.cart.friction, cfg.pole.friction) * 12)
-
-
-def solve_bytes(info, cfg):
-    """Algorithmic bytes k_solve moves per env (fp32): the record header (32 words) and its live
-    rows (8 / 12 words per one- / two-body row) in; iteration count, velocity deltas and normal
-    impulses (25 words) out."""
-    return 4.0 * (32 + _row_words(info, cfg) + 25)
-
-
-def prep_bytes(info, cfg, RS):
-    """Algorithmic bytes k_prep moves per env and launch, averaged over the RS + 1 launches of a
-    call: the env record (164 floats + 8 ints) in and out every launch; RS of them write a solve
-    record (header + live rows) and RS read one back (header) and the action; the last writes the
-    (R,2,7) observation, reward, done and reason."""
-    state = 2.0 * (164 * 4 + 8 * 4)
-    setup = 4.0 * (32 + _row_words(info, cfg))
-    finish = 4.0 * 32 + 8.0
-    close = cfg.action_repeats * 14 * 4 + 6.0
-    return state + (RS * (setup + finish) + close) / (RS + 1)
+def algorithmic_bytes_per_env_step(cfg):
+    state = (26 + 6 + 3 * 4 * 11) * 4 + 8 * 4
+    action = 4 if cfg.discrete_actions else 8
+    return 2 * state + action + cfg.action_repeats * 56 + 4 + 1 + 1
 
 
 # ---------------------------------------------------------------------------------------
@@ -193,6 +183,39 @@ class ClockSampler(threading.Thread):
 
 
 # ---------------------------------------------------------------------------------------
+# BASELINE.json configs[3]: 1 M envs sharded over the ranks, --initial-force=55, episode-length deciles
+# ---------------------------------------------------------------------------------------
+def run_configs3(args, rank, world, local):
+    """This rank's shard of configs[3]: envs [rank*B/G, (rank+1)*B/G) of B = 1 048 576 continuous envs with
+    --initial-force=55 play ONE episode each under the in-kernel random agent (bcp_rollout_random: actions drawn from
+    Philox keyed by GLOBAL env id, so the episodes do not depend on the sharding).  Returns the shard's histogram and
+    counters; the caller merges them in the bench's single all_reduce."""
+    import torch
+    from cartpoleplusplus_b200.env import BatchedBulletCartpole
+    from cartpoleplusplus_b200.parallel import shard
+    total = args.configs3_envs
+    off, n = shard(total, rank, world)
+    opts = default_opts(action_force=100.0, initial_force=55.0, auto_reset="pipelined")
+    env = BatchedBulletCartpole(opts, discrete_actions=False, num_envs=n, device=local, dtype=args.dtype, seed=args.seed, env_id_offset=off)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    header = {"episodes": 0}
+    calls = 0
+    while header["episodes"] < n and calls < 64:   # reset (65 calls of R*S substeps) + at most 200 steps per episode
+        env.rollout_random(64, max_episodes=1)
+        calls += 1
+        hist, header, rsum = env.stats()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    if header["episodes"] != n:
+        raise RuntimeError(f"configs[3]: {header['episodes']} of {n} episodes finished")
+    env.close()
+    return {"hist": hist, "episodes": header["episodes"], "env_steps": header["env_steps"], "reward_sum": rsum, "ms": ms, "envs_total": total}
+
+
+# ---------------------------------------------------------------------------------------
 # the measured arm
 # ---------------------------------------------------------------------------------------
 def run_ours(args):
@@ -217,7 +240,7 @@ def run_ours(args):
     RS = env.cfg.action_repeats * env.cfg.steps_per_repeat
     gen = torch.Generator(device=dev)
     gen.manual_seed(args.seed + rank)
-    pool = torch.rand((W + K, n, 2), device=dev, generator=gen) * 2 - 1  # inputs resident in HBM
+    pool = torch.rand((min(W + K, 64), n, 2), device=dev, generator=gen) * 2 - 1  # inputs resident in HBM (cycled)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > L2 (126 MB)
     env.reset(copy=False)
     # untimed: roll the batch to its stationary mix of episode phases (random agent, in-kernel actions)
@@ -228,14 +251,13 @@ def run_ours(args):
         flush.zero_()  # untimed L2 flush between steps
         if ev:
             ev[0].record()
-        env.step(pool[t], copy=False)
+        env.step(pool[t % len(pool)], copy=False)
         if ev:
             ev[1].record()
 
     for t in range(W):
         one_step(t)
     torch.cuda.synchronize()
-    env.clear_stats()
     launches0 = env.launch_count
     try:
         uuid = str(torch.cuda.get_device_properties(local).uuid)
@@ -244,21 +266,35 @@ def run_ours(args):
         uuid = None
     sampler = ClockSampler(local, uuid)  # runs through both timed regions (device-timed steps, then e2e)
     sampler.start()
-    env.profile_begin()
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    # The batch's episode phases move in waves (every env was reset together; the mix calls decorrelate them only
+    # partly), so a short contiguous window reads high or low depending on where it falls (round 1: 1.38e8 over 20
+    # steps, 1.20e8 over 200).  The K timed steps are therefore spread over a fixed span of >= 200 env.steps: between
+    # two timed steps the batch advances `stride - 1` untimed steps (same call, same inputs, not timed, not counted).
+    stride = max(1, -(-args.span // K))
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(K)]
+    live_acc = torch.zeros((), dtype=torch.float64, device=dev)   # env.steps taken by the TIMED calls (reward 1), summed on the device
+    t_all = W
+    env.clear_stats()
+    env.profile_begin()   # brackets every kernel of every call of the span: per-launch averages
     for t in range(K):
-        one_step(W + t, evs[t])
+        for _ in range(stride - 1):
+            one_step(t_all)
+            t_all += 1
+        one_step(t_all, evs[t])
+        live_acc += env.reward.sum()
+        t_all += 1
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
     prof = env.profile_end()
+    calls = K * stride
+    hist, header, _ = env.stats()   # episode statistics of the whole span
+    live_steps = int(round(float(live_acc.item())))
     total_ms = sum(e[0].elapsed_time(e[1]) for e in evs)
-    launches = env.launch_count - launches0
-    hist, header, _ = env.stats()
-    live_steps = header["env_steps"]
+    launches = (env.launch_count - launches0) // stride
 
     # ---- e2e: same metric through step_host (pinned host buffers, H2D + D2H inside) ----
     host_actions = [torch.empty((n, 2), dtype=torch.float32).pin_memory() for _ in range(2)]
@@ -279,37 +315,37 @@ def run_ours(args):
     e2e_s = time.perf_counter() - t0
     sampler.stop_flag = True
 
-    # ---- max over ranks of the times, sums of the counts; the one collective: statistics allreduce ----
-    tt = torch.tensor([total_ms, e2e_s * 1e3], dtype=torch.float64, device=dev)
-    cc = torch.tensor([live_steps, e2e_live, header["episodes"]], dtype=torch.int64, device=dev)
-    hist_t = torch.from_numpy(hist).to(dev)
+    # ---- configs[3] (N >= 2 only): 1 048 576 envs sharded over the ranks, --initial-force=55, a fixed episode budget (one
+    # episode per env) through bcp_rollout_random; its statistics ride in the same single collective below ----
+    c3 = None
+    if world > 1 and not args.no_configs3:
+        c3 = run_configs3(args, rank, world, local)
+
+    # ---- THE one collective of the path: a single all_reduce(SUM) of float64 - per-rank time slots (max taken locally),
+    # counts, the episode-length histograms and the reward sum (all exact below 2^53) ----
+    nb = env.max_episode_len + 1
+    slots = np.zeros(3 * world)
+    slots[3 * rank:3 * rank + 3] = [total_ms, e2e_s * 1e3, c3["ms"] if c3 else 0.0]
+    counts = [live_steps, e2e_live, header["episodes"]] + ([c3["episodes"], c3["env_steps"], c3["reward_sum"]] if c3 else [0, 0, 0.0])
+    packed = torch.from_numpy(np.concatenate([slots, counts, hist.astype(np.float64), c3["hist"].astype(np.float64) if c3 else np.zeros(nb)])).to(dev)
     if world > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dist.all_reduce(cc, op=dist.ReduceOp.SUM)
-        dist.all_reduce(hist_t, op=dist.ReduceOp.SUM)
-    total_ms, e2e_ms = (float(v) for v in tt.tolist())
-    live_all, e2e_live_all, episodes_all = (int(v) for v in cc.tolist())
+        dist.all_reduce(packed, op=dist.ReduceOp.SUM)
+    packed = packed.cpu().numpy()
+    slots = packed[:3 * world].reshape(world, 3)
+    total_ms, e2e_ms, c3_ms = (float(slots[:, k].max()) for k in range(3))
+    live_all, e2e_live_all, episodes_all, c3_eps, c3_steps = (int(round(v)) for v in packed[3 * world:3 * world + 5])
+    c3_rsum = float(packed[3 * world + 5])
+    hist_all = np.rint(packed[3 * world + 6:3 * world + 6 + nb]).astype(np.int64)
+    c3_hist = np.rint(packed[3 * world + 6 + nb:]).astype(np.int64)
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- census of the batch: what the solves of the last substep did (contact points per pair,
-    # PGS iterations), read back from the pipeline's own solve records on the GPU ----
+    # ---- census: what every env's solve did in each of the R*S substeps of one more (untimed) call, read back from the
+    # pipeline's own solve records on the GPU (bcp_solve_trace) ----
     split = prof["n_solve"] > 0
-    if split:
-        li = env.last_solve_info().astype(np.int64)                       # (n, 4): gc, cp, gp points, iterations
-        busy = ((env.reward > 0) | (env.reason == C.REASON_RESETTING)).cpu().numpy()   # envs that ran that substep
-        info = np.zeros((n, 6), dtype=np.int64)
-        info[:, 0] = li[:, 3]
-        info[:, 3:6] = li[:, 0:3]
-        info[~busy] = 0
-        iters = float(info[busy, 0].mean()) if busy.any() else 0.0
-        rows_gc, rows_cp, rows_gp = (float(info[busy, 3 + k].mean()) for k in range(3))
-        flops_env = float(solve_flops(info, env.cfg).mean())
-        bytes_env = float(solve_bytes(info, env.cfg).mean())
-    else:  # the one-launch kernels keep no per-env solve record: no census, no flop view
-        info, busy, iters, rows_gc, rows_cp, rows_gp, flops_env, bytes_env = None, None, None, None, None, None, None, None
+    model_name, model = load_flops_model(env.cfg)
     lib = _lib.load()
     peak32, peak64 = ctypes.c_double(), ctypes.c_double()
     lib.bcp_bench_fma_peak(local, 0, 4096, ctypes.byref(peak32))
@@ -326,28 +362,44 @@ def run_ours(args):
         traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
     except Exception:
         pass
-    # per kernel: algorithmic bytes of one launch / its average launch time in the timed region
-    kernels = {}
+    kernels, census = {}, None
     if split:
-        pb = float(prep_bytes(info, env.cfg, RS).mean())
-        kernels["k_prep"] = {"ms_per_step": prof["ms_prep"] / K, "launch_ms": prof["ms_prep"] / max(1, prof["n_prep"]),
-                             "bytes_per_env_launch": pb, "bytes_per_launch": pb * n}
-        kernels["k_solve"] = {"ms_per_step": prof["ms_solve"] / K, "launch_ms": prof["ms_solve"] / max(1, prof["n_solve"]),
-                              "bytes_per_env_launch": bytes_env, "bytes_per_launch": bytes_env * n}
-    else:
-        kernels["k_step"] = {"ms_per_step": prof["ms_prep"] / K, "launch_ms": prof["ms_prep"] / max(1, prof["n_prep"]),
-                             "bytes_per_env_launch": 2.0 * 176 * 8 + 8, "bytes_per_launch": (2.0 * 176 * 8 + 8) * n}
+        env.solve_trace(True)
+        one_step(t_all)
+        torch.cuda.synchronize()
+        tr = env.solve_trace().astype(np.int64)                      # (RS, n, 4): gc, cp, gp points, iterations
+        busy = ((env.reward > 0) | (env.reason == C.REASON_RESETTING) | (env.reason == C.REASON_FRESH)).cpu().numpy()
+        env.solve_trace(False)
+        cnt = tr[:, busy, :].reshape(-1, 4)
+        fixed, pgs = substep_flops(model, cnt)
+        busy_frac = float(busy.mean())
+        flops_call = float(fixed.sum() + pgs.sum())                   # one env.step of the whole batch (this rank)
+        census = {"source": "bcp_solve_trace: every env's solve record in each substep of one more call after the timed span",
+                  "busy_fraction": busy_frac, "mean_solver_iterations": float(cnt[:, 3].mean()),
+                  "mean_contact_points": {"ground_cart": float(cnt[:, 0].mean()), "cart_pole": float(cnt[:, 1].mean()), "ground_pole": float(cnt[:, 2].mean())},
+                  "flops_per_busy_substep": {"fixed": float(fixed.mean()), "pgs": float(pgs.mean())},
+                  "flops_model": f"profiles/flops_model.json[{model_name}] (counted on the parity substep, FMA = 2)"}
+        kernels["k_prep"] = {"ms_per_step": prof["ms_prep"] / calls, "launch_ms": prof["ms_prep"] / max(1, prof["n_prep"]),
+                             "flops_per_step": float(fixed.sum()), "what": "narrowphase, manifolds, dynamics, row setup, integrate"}
+        kernels["k_solve"] = {"ms_per_step": prof["ms_solve"] / calls, "launch_ms": prof["ms_solve"] / max(1, prof["n_solve"]),
+                              "flops_per_step": float(pgs.sum()), "what": "projected Gauss-Seidel (k_solve_lam + k_solve_tail + side-stream k_solve)"}
+    else:  # the one-launch kernels keep no per-env solve record: the model's workload mean stands in
+        flops_call = model["mean_flops_per_substep"] * RS * n
+        kernels["k_step"] = {"ms_per_step": prof["ms_prep"] / calls, "launch_ms": prof["ms_prep"] / max(1, prof["n_prep"]),
+                             "flops_per_step": flops_call, "what": "whole env.step in one launch"}
+    step_ms = total_ms / K
     for name, kd in kernels.items():
-        kd["achieved_gbs"] = kd["bytes_per_launch"] / (kd["launch_ms"] * 1e-3) / 1e9
-        kd["frac_of_hbm_peak"] = kd["achieved_gbs"] / hbm_peak
-        kd["share_of_step"] = kd["ms_per_step"] * K / total_ms
+        kd["achieved_tflops"] = kd["flops_per_step"] / (kd["ms_per_step"] * 1e-3) / 1e12
+        kd["frac_of_fp32_peak"] = kd["achieved_tflops"] / pipe_peak
+        kd["share_of_step"] = kd["ms_per_step"] / step_ms
         t = traffic.get(name if args.dtype == "fp32" else name + "_f64")
-        kd["traffic"] = t.get("bytes_per_launch") if isinstance(t, dict) and int(t.get("num_envs", n)) == n else None
+        kd["dram_bytes_per_launch_ncu"] = t.get("bytes_per_launch") if isinstance(t, dict) and int(t.get("num_envs", n)) == n else None
     dom_name = max(kernels, key=lambda k: kernels[k]["ms_per_step"])
     dom = kernels[dom_name]
-    solve_name = "k_solve" if split else "k_step"
-    solve_ms = kernels[solve_name]["launch_ms"]
-    achieved_tf = flops_env * n / (solve_ms * 1e-3) / 1e12 if split else None
+    alg_bytes = algorithmic_bytes_per_env_step(env.cfg) * n * busy_frac if split else algorithmic_bytes_per_env_step(env.cfg) * n
+    t_step = traffic.get("env_step") if args.dtype == "fp32" else None
+    dram_step = t_step.get("bytes_per_step") if isinstance(t_step, dict) and int(t_step.get("num_envs", n)) == n else None
+    whole_tf = flops_call / (step_ms * 1e-3) / 1e12
     value = live_all / (total_ms * 1e-3)
     out = {
         "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
@@ -360,37 +412,49 @@ def run_ours(args):
                    "auto_reset": "pipelined: a finished env runs its 130-substep reset R*S substeps per call; only env.steps "
                                  "actually taken are counted",
                    "phase_mix": f"stationary ({args.mix_calls} untimed random-agent calls before timing)",
+                   "window": f"the {K} timed steps are every {stride}th env.step of a span of {calls} (episode phases move in waves; "
+                             "the steps in between run untimed and uncounted)" if stride > 1 else f"{K} consecutive env.steps",
                    "l2": "flushed between steps (256 MiB memset, untimed)", "parallelism": f"env-sharded x{world}", "pipeline": env.solver_kind,
                    "seed": args.seed},
         "live_fraction": live_all / (world * n * K),
         "slot_steps_per_s": world * n * K / (total_ms * 1e-3),
         "substeps_per_s": world * n * K * RS / (total_ms * 1e-3),
-        "episodes_finished": episodes_all,
-        "mean_episode_len": float((hist_t.cpu().numpy() * np.arange(len(hist))).sum() / max(1, int(hist_t.sum().item()))),
+        "episodes_finished_in_span": episodes_all,
+        "mean_episode_len": float((hist_all * np.arange(len(hist_all))).sum() / max(1, int(hist_all.sum()))),
         "kernel_ms_per_step": {k: v["ms_per_step"] for k, v in kernels.items()},
         "e2e": {"value": e2e_live_all / (e2e_ms * 1e-3), "unit": "env-steps/s",
                 "h2d_bytes_per_step": env.h2d_bytes_per_step, "d2h_bytes_per_step": env.d2h_bytes_per_step},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
-        # the dominant kernel (largest share of the step) against the measured HBM copy bandwidth
-        "roofline": {"bound": "hbm", "achieved": dom["achieved_gbs"], "peak": hbm_peak, "unit": "GB/s",
-                     "frac": dom["frac_of_hbm_peak"], "traffic": dom["traffic"], "kernel": dom_name,
+        # BASELINE.json's metric is "% FP32 peak": the path is bound by the FP32 CUDA-core pipe (no contraction, arithmetic
+        # intensity far above the ridge), so the roofline is flops - counted, algorithmic - over the measured FMA peak.
+        "roofline": {"bound": "fp32", "kernel": dom_name, "achieved": dom["achieved_tflops"], "peak": pipe_peak, "unit": "TFLOP/s",
+                     "frac": dom["frac_of_fp32_peak"], "whole_step_frac": whole_tf / pipe_peak, "whole_step_achieved": whole_tf,
                      "launch_ms": dom["launch_ms"], "share_of_step": dom["share_of_step"],
-                     "algorithmic_bytes_per_env_launch": dom["bytes_per_env_launch"],
-                     "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s",
-                     "note": "both kernels are issue-latency bound, not bandwidth bound (profiles/); "
-                             "see roofline_kernels and roofline_pipe"},
+                     "flops_per_env_step_call": flops_call / n,
+                     "peak_source": "bcp_bench_fma_peak (dependent-free FMA chains on every SM, measured in this run; "
+                                    "MEASURED_PEAKS.json has no CUDA-core entry)",
+                     # DRAM bytes of ALL launches of one env.step (ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum,
+                     # profiles/traffic.json) beside SURVEY 8d's algorithmic bytes (state once in, once out, action, outputs)
+                     "traffic": dram_step, "algorithmic_bytes": alg_bytes,
+                     "traffic_ratio": (dram_step / alg_bytes) if dram_step else None,
+                     "hbm": {"achieved_gbs": alg_bytes / (step_ms * 1e-3) / 1e9, "peak_gbs": hbm_peak,
+                             "frac": alg_bytes / (step_ms * 1e-3) / 1e9 / hbm_peak,
+                             "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback 6650 GB/s"}},
         "roofline_kernels": kernels,
-        "roofline_pipe": None if not split else {
-            "bound": "fp32-cuda-core", "kernel": solve_name,
-            "launch_ms": solve_ms, "share_of_step": kernels[solve_name]["share_of_step"],
-            "achieved": achieved_tf, "peak": pipe_peak, "unit": "TFLOP/s", "frac": achieved_tf / pipe_peak,
-            "peak_source": "bcp_bench_fma_peak (FMA chains, measured in this run)",
-            "flops_per_env_solve": flops_env, "bytes_per_env_solve": bytes_env,
-            "mean_solver_iterations": iters, "busy_fraction": float(busy.mean()),
-            "mean_rows": {"ground_cart": rows_gc, "cart_pole": rows_cp, "ground_pole": rows_gp},
-            "census": "bcp_last_solve_info: every env's solve record after the last timed call"},
+        "census": census,
     }
+    if c3:
+        from cartpoleplusplus_b200 import protocol
+        import hashlib
+        out["configs3"] = {
+            "workload": "configs[3]: 1 048 576 envs continuous sharded over the ranks, --initial-force=55, one episode per env "
+                        "(bcp_rollout_random, in-kernel Philox actions keyed by global env id), one allreduce",
+            "envs_total": c3["envs_total"], "envs_per_gpu": c3["envs_total"] // world, "episodes": c3_eps, "env_steps": c3_steps,
+            "value": c3_steps / (c3_ms * 1e-3), "unit": "env-steps/s", "ms": c3_ms, "reward_sum": c3_rsum,
+            "deciles": [float(x) for x in protocol.deciles_from_histogram(c3_hist)],
+            "histogram_sha256": hashlib.sha256(c3_hist.astype("<i8").tobytes()).hexdigest(),
+            "note": "trajectories are keyed by global env id: deciles and hash must be identical for every N"}
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(args)
     print(json.dumps(out))
@@ -466,6 +530,9 @@ def main():
     ap.add_argument("--steps-per-repeat", type=int, default=1)
     ap.add_argument("--cart-friction", type=float, default=None, help="override cart.urdf's lateral_friction (0.0)")
     ap.add_argument("--mix-calls", type=int, default=400, help="untimed random-agent calls before timing")
+    ap.add_argument("--span", type=int, default=200, help="env.steps the timed steps are spread over (>= --steps: every span/steps-th step is timed)")
+    ap.add_argument("--no-configs3", action="store_true", help="N >= 2: skip the configs[3] run (1 M envs sharded, deciles)")
+    ap.add_argument("--configs3-envs", type=int, default=1048576)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

@@ -40,13 +40,16 @@ BCP_HD_NOINLINE void substep(const Params<T>& P, Env<T>& st, SubstepInfo* info) 
     const Posed<T>& B = box[pairB[m]];
     T ws[kBoxWs];
     const Contact<T>* cs = box_contacts(ws);
+    census_phase<T>(CENSUS_NARROWPHASE);
     const int nc = box_box(A.x, A.R, A.h, B.x, B.R, B.h, ws);
+    census_phase<T>(CENSUS_MANIFOLD);
     for (int k = 0; k < nc; ++k) manifold_add(st.mani[m], A, B, cs[k], P.breaking[m]);
     manifold_refresh(st.mani[m], A, B, P.breaking[m], wp[m]);
     if (info) info->contacts[m] = st.mani[m].count;
   }
 
   // ---- 2. gravity + external force -> unconstrained velocities ----
+  census_phase<T>(CENSUS_DYNAMICS);
   bodies[0].dyn = 0;
   bodies[0].mass = bodies[0].inv_mass = 0;
   for (int i = 0; i < 3; ++i) { bodies[0].x[i] = box[0].x[i]; bodies[0].I[i] = 0; }
@@ -69,6 +72,7 @@ BCP_HD_NOINLINE void substep(const Params<T>& P, Env<T>& st, SubstepInfo* info) 
   }
 
   // ---- 3. contact rows, manifolds in post-island-sort order ----
+  census_phase<T>(CENSUS_ROWS);
   for (int k = 0; k < 3; ++k) {
     const int m = (P.manifold_order == 0) ? 2 - k : k;
     const Manifold<T>& mf = st.mani[m];
@@ -101,6 +105,7 @@ BCP_HD_NOINLINE void substep(const Params<T>& P, Env<T>& st, SubstepInfo* info) 
   }
 
   // ---- 4. projected Gauss-Seidel sweep with least-squares-residual early exit ----
+  census_phase<T>(CENSUS_PGS);
   int it = 0;
   for (; it < P.solver_iterations; ++it) {
     T lsr = 0;
@@ -148,6 +153,7 @@ BCP_HD_NOINLINE void substep(const Params<T>& P, Env<T>& st, SubstepInfo* info) 
   }
 
   // ---- 5. velocities += deltas; integrate transforms ----
+  census_phase<T>(CENSUS_INTEGRATE);
   for (int k = 0; k < 2; ++k) {
     SBody<T>& b = bodies[k + 1];
     Body<T>& o = k == 0 ? st.cart : st.pole;

@@ -32,6 +32,11 @@ template <> struct Lim<double> {
   static BCP_HD double large() { return 1e18; }
 };
 
+// Flop census hook: tests/host_harness/flopcount.cpp instantiates the parity substep with a counting scalar and
+// specialises this to attribute the operations to a phase of the substep; for float and double it is nothing.
+enum { CENSUS_NARROWPHASE = 0, CENSUS_MANIFOLD, CENSUS_DYNAMICS, CENSUS_ROWS, CENSUS_PGS, CENSUS_INTEGRATE, CENSUS_PHASES };
+template <typename T> BCP_HD void census_phase(int) {}
+
 BCP_HD float bsqrt(float x) { return sqrtf(x); }
 BCP_HD double bsqrt(double x) { return sqrt(x); }
 BCP_HD float babs(float x) { return fabsf(x); }

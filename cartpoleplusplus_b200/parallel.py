@@ -34,15 +34,14 @@ def allreduce_stats_arrays(hist: np.ndarray, header: np.ndarray, reward_sum: flo
         return hist.copy(), header.copy(), float(reward_sum)
     if device is None:
         device = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
-    # the counts travel as int64 (exact); the reward sum rides along as its float64 bit pattern
-    # is not summable, so it goes in a second, 1-element float64 reduce fused by the coalescing
-    # manager when available - two tiny messages at worst
-    packed = torch.from_numpy(np.concatenate([hist, header])).to(device)
-    rs = torch.tensor([reward_sum], dtype=torch.float64, device=device)
+    # ONE message: counts and the reward sum travel together as float64 (the counts stay exact below 2^53)
+    if max(int(hist.sum()), int(np.abs(header).max(initial=0))) >= 2 ** 53:
+        raise OverflowError("statistics beyond 2^53 do not travel exactly as float64")
+    packed = torch.from_numpy(np.concatenate([hist.astype(np.float64), header.astype(np.float64), [float(reward_sum)]])).to(device)
     dist.all_reduce(packed, op=dist.ReduceOp.SUM)
-    dist.all_reduce(rs, op=dist.ReduceOp.SUM)
     packed = packed.cpu().numpy()
-    return packed[:hist.size].copy(), packed[hist.size:].copy(), float(rs.item())
+    nh, nd = hist.size, header.size
+    return np.rint(packed[:nh]).astype(np.int64), np.rint(packed[nh:nh + nd]).astype(np.int64), float(packed[nh + nd])
 
 
 def allreduce_stats(env):
