@@ -49,8 +49,28 @@ struct bcp_env {
   int* list = nullptr;   // compacted env indices for masked resets
   int* count = nullptr;
   double* staging = nullptr;  // canonical records for get/set_state
-  bcp::SplitBuffers split = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};  // solve records / queue of the split pipeline
+  // Split pipeline.  The envs of a handle run as `cohorts` independent pipelines over disjoint env ranges, each on its
+  // own stream: k_prep and the solve phase are both latency-bound, and one cohort's solve tail (a few warps iterating)
+  // leaves most issue slots to the other cohort's k_prep.  Every per-env array is env-major, so a cohort's state,
+  // records and outputs are offset views of the handle's; queue, counters, bins and continuation buffers are its own.
+  struct Cohort {
+    int base = 0, n = 0;
+    bcp::Params<float> P;
+    bcp::SplitBuffers b = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, -1};
+    cudaStream_t stream = nullptr;   // cohort 0 runs on the caller's stream
+    cudaEvent_t ev_done = nullptr;
+    std::vector<cudaEvent_t> ev_prep;  // bcp_step_host: after the k-th k_prep of the call
+  };
+  std::vector<Cohort> cohorts;
+  cudaEvent_t ev_fork = nullptr;
+  float* recs = nullptr;   // solve records of every env, [N][record words]
+  int* trace = nullptr;    // bcp_solve_trace_*: [R*S][N][4]
   int use_split = 0;
+  int use_lam = 0;
+  // bcp_step_host's hook into the cohorts' launch sequences
+  struct HookArg { bcp_env* h; int cohort; };
+  void (*split_hook)(void* ctx, int k, cudaStream_t s) = nullptr;
+  std::vector<HookArg> hook_args;
   // bcp_step_host: device-side actions / outputs / packed observation slabs, the copy stream
   struct HostStep {
     void* d_act = nullptr;
@@ -149,15 +169,43 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
     // the pooled solver implements the default row order and the two-direction friction cone
     if (cfg->manifold_order != 0 || cfg->friction_dirs != 2 || !cfg->cone_friction) h->use_split = 0;
     if (h->use_split) {
-      A((void**)&h->split.recs, bcp::split_record_words(h->p32) * N * sizeof(float));
-      A((void**)&h->split.queue, N * 4 * sizeof(int));  // {env, contact counts} per entry; main queue, then the generic one
-      A((void**)&h->split.qc, bcp::split_counter_words(h->p32) * sizeof(int));
-      A((void**)&h->split.cont, bcp::split_cont_words(h->p32) * sizeof(float));
-      A((void**)&h->split.contm, N * 4 * sizeof(int));
-      for (int k = 0; k < 2; ++k) {
-        A((void**)&h->split.bins[k], bcp::split_bins_words(h->p32) * sizeof(int));
-        A((void**)&h->split.cnts[k], 8 * sizeof(int));
+      const size_t rw = bcp::split_record_words(h->p32);
+      A((void**)&h->recs, rw * N * sizeof(float));
+      h->use_lam = bcp::split_uses_lambda(h->p32) ? 1 : 0;
+      // two cohorts from 32 768 envs up (measured on B200: 65 536 envs as 2 x 32 768 on two streams 0.348 -> 0.298 ms
+      // per env.step, 4 x 16 384 the same; 131 072 as 2 x 65 536 0.589 -> 0.513); BCP_COHORTS overrides
+      const char* cv = getenv("BCP_COHORTS");
+      int nc = cv ? atoi(cv) : (cfg->num_envs >= 32768 ? 2 : 1);
+      if (nc < 1) nc = 1;
+      if (nc > 8) nc = 8;
+      while (nc > 1 && cfg->num_envs / nc < 1024) nc--;
+      h->cohorts.resize(nc);
+      for (int c = 0; c < nc && err == cudaSuccess; ++c) {
+        bcp_env::Cohort& co = h->cohorts[c];
+        co.base = (int)((long long)cfg->num_envs * c / nc) & ~127;           // whole blocks, 16-byte aligned outputs
+        const int end = (c == nc - 1) ? cfg->num_envs : ((int)((long long)cfg->num_envs * (c + 1) / nc) & ~127);
+        co.n = end - co.base;
+        co.P = h->p32;
+        co.P.num_envs = co.n;
+        co.P.env_id_offset = h->p32.env_id_offset + co.base;
+        const size_t n = (size_t)co.n;
+        co.b.recs = h->recs + (size_t)co.base * rw;
+        co.b.lam = h->use_lam;
+        co.b.trace_stride = cfg->num_envs;
+        A((void**)&co.b.queue, n * 4 * sizeof(int));  // {env, contact counts} per entry; main queue, then the generic one
+        A((void**)&co.b.qc, bcp::split_counter_words(co.P) * sizeof(int));
+        A((void**)&co.b.cont, bcp::split_cont_words(co.P) * sizeof(float));
+        A((void**)&co.b.contm, n * 4 * sizeof(int));
+        for (int k = 0; k < 2; ++k) {
+          A((void**)&co.b.bins[k], bcp::split_bins_words(co.P) * sizeof(int));
+          A((void**)&co.b.cnts[k], 8 * sizeof(int));
+        }
+        if (c > 0 && err == cudaSuccess) {
+          err = cudaStreamCreateWithFlags(&co.stream, cudaStreamNonBlocking);
+          if (err == cudaSuccess) err = cudaEventCreateWithFlags(&co.ev_done, cudaEventDisableTiming);
+        }
       }
+      if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
     }
   }
   if (err != cudaSuccess) {
@@ -177,10 +225,17 @@ int bcp_destroy(bcp_env* h) {
     cudaFree(h->hs.d_act); cudaFree(h->hs.d_out); cudaFree(h->hs.d_slab);
     cudaStreamDestroy(h->hs.copy); cudaEventDestroy(h->hs.ev_ready); cudaEventDestroy(h->hs.ev_copied); if (h->hs.ev_h2d) cudaEventDestroy(h->hs.ev_h2d);
   }
-  if (h->split.side) { cudaStreamDestroy(h->split.side); cudaEventDestroy(h->split.ev_prep); cudaEventDestroy(h->split.ev_gen); }
-  cudaFree(h->split.trace);
-  cudaFree(h->split.recs); cudaFree(h->split.queue); cudaFree(h->split.qc); cudaFree(h->split.cont); cudaFree(h->split.contm);
-  for (int k = 0; k < 2; ++k) { cudaFree(h->split.bins[k]); cudaFree(h->split.cnts[k]); }
+  for (bcp_env::Cohort& co : h->cohorts) {
+    if (co.b.side) { cudaStreamDestroy(co.b.side); cudaEventDestroy(co.b.ev_prep); cudaEventDestroy(co.b.ev_gen); }
+    cudaFree(co.b.queue); cudaFree(co.b.qc); cudaFree(co.b.cont); cudaFree(co.b.contm);
+    for (int k = 0; k < 2; ++k) { cudaFree(co.b.bins[k]); cudaFree(co.b.cnts[k]); }
+    if (co.stream) cudaStreamDestroy(co.stream);
+    if (co.ev_done) cudaEventDestroy(co.ev_done);
+    for (cudaEvent_t e : co.ev_prep) cudaEventDestroy(e);
+  }
+  if (h->ev_fork) cudaEventDestroy(h->ev_fork);
+  cudaFree(h->trace);
+  cudaFree(h->recs);
   delete h;
   return 0;
 }
@@ -209,10 +264,32 @@ int bcp_step(bcp_env* h, const void* actions, float* obs_out, float* reward_out,
   cudaStream_t s = (cudaStream_t)stream;
   if (!h->f64() && h->use_split) {
     int n = 0;
-    const size_t ev0 = h->prof_events.size();
-    CK(bcp::launch_step_split(h->p32, (float*)h->fdata, h->idata, h->split, actions, obs_out, reward_out, done_out, reason_out, h->stats(), s, &n,
-                              h->profiling ? &h->prof_events : nullptr));
-    if (h->profiling) h->prof_calls.push_back((int)(h->prof_events.size() - ev0));
+    const int width = 14 * h->cfg.action_repeats;
+    const size_t abytes = h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float);
+    // while the kernels are being bracketed by events (bcp_profile_begin) the cohorts run one after the other on the
+    // caller's stream, so that a kernel's time is its own
+    const bool fork = h->cohorts.size() > 1 && !h->profiling;
+    if (fork) CK(cudaEventRecord(h->ev_fork, s));
+    for (size_t c = 0; c < h->cohorts.size(); ++c) {
+      bcp_env::Cohort& co = h->cohorts[c];
+      cudaStream_t cs = (fork && c > 0) ? co.stream : s;
+      if (fork && c > 0) CK(cudaStreamWaitEvent(cs, h->ev_fork, 0));
+      const size_t b = (size_t)co.base;
+      const size_t ev0 = h->prof_events.size();
+      co.b.trace = h->trace ? h->trace + b * 4 : nullptr;
+      co.b.after_prep = h->split_hook;
+      co.b.hook_ctx = h->split_hook ? &h->hook_args[c] : nullptr;
+      CK(bcp::launch_step_split(co.P, (float*)h->fdata + b * bcp::NF, h->idata + b * bcp::NI, co.b,
+                                static_cast<const char*>(actions) + b * abytes, obs_out ? obs_out + b * width : nullptr,
+                                reward_out ? reward_out + b : nullptr, done_out ? done_out + b : nullptr,
+                                reason_out ? reason_out + b : nullptr, h->stats(), cs, &n,
+                                h->profiling ? &h->prof_events : nullptr));
+      if (h->profiling) h->prof_calls.push_back((int)(h->prof_events.size() - ev0));
+      if (fork && c > 0) {
+        CK(cudaEventRecord(co.ev_done, cs));
+        CK(cudaStreamWaitEvent(s, co.ev_done, 0));
+      }
+    }
     h->launches += n;
     return 0;
   }
@@ -241,17 +318,28 @@ void pack_and_copy(bcp_env* h, int r, cudaStream_t s) {
   cudaMemcpyAsync(h->hs.h_obs + (size_t)r * n * 14, slab, (size_t)n * 14 * sizeof(float), cudaMemcpyDeviceToHost, s);
   h->launches++;
 }
-// after the k-th k_prep of a split call: repeat r = k / S - 1 is complete when k is a multiple of S
+// after the k-th k_prep of a cohort's call has been enqueued on its stream `s`: repeat r = k / S - 1 is complete for
+// that cohort when k is a multiple of S.  The cohorts are enqueued one after the other, so the LAST cohort's hook is the
+// point at which every cohort's event for k exists: the copy stream waits for all of them, packs the slab and copies it.
 void host_step_hook(void* ctx, int k, cudaStream_t s) {
-  bcp_env* h = static_cast<bcp_env*>(ctx);
+  bcp_env::HookArg* a = static_cast<bcp_env::HookArg*>(ctx);
+  bcp_env* h = a->h;
   const int R = h->cfg.action_repeats, S = h->cfg.steps_per_repeat;
+  const bool last = a->cohort == (int)h->cohorts.size() - 1;
   if (k == 0 && h->hs.h2d_pending) {
     cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);  // every later kernel of the call reads the actions
-    h->hs.h2d_pending = false;
+    if (last) h->hs.h2d_pending = false;
   }
   if (k <= 0 || k >= R * S || k % S) return;  // the last repeat leaves with the call's other outputs
-  cudaEventRecord(h->hs.ev_ready, s);
-  cudaStreamWaitEvent(h->hs.copy, h->hs.ev_ready, 0);
+  bcp_env::Cohort& co = h->cohorts[a->cohort];
+  while ((int)co.ev_prep.size() <= k) {
+    cudaEvent_t e;
+    cudaEventCreateWithFlags(&e, cudaEventDisableTiming);
+    co.ev_prep.push_back(e);
+  }
+  cudaEventRecord(co.ev_prep[k], s);
+  if (!last) return;
+  for (bcp_env::Cohort& c : h->cohorts) cudaStreamWaitEvent(h->hs.copy, c.ev_prep[k], 0);
   pack_and_copy(h, k / S - 1, h->hs.copy);
   cudaEventRecord(h->hs.ev_copied, h->hs.copy);
   h->hs.fired = true;
@@ -299,9 +387,13 @@ int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_r
   }
   h->hs.h_obs = h_obs_rm;
   h->hs.fired = false;
-  if (split) { h->split.after_prep = host_step_hook; h->split.hook_ctx = h; }
+  if (split) {
+    h->hook_args.resize(h->cohorts.size());
+    for (size_t c = 0; c < h->cohorts.size(); ++c) h->hook_args[c] = bcp_env::HookArg{h, (int)c};
+    h->split_hook = host_step_hook;
+  }
   const int rc = bcp_step(h, h->hs.d_act, d_obs, d_rew, d_done, d_reason, stream);
-  h->split.after_prep = nullptr;
+  h->split_hook = nullptr;
   if (h->hs.h2d_pending) {  // the call failed before its first kernel
     cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);
     h->hs.h2d_pending = false;
@@ -442,8 +534,8 @@ int64_t bcp_launch_count(const bcp_env* h) { return h ? h->launches : 0; }
 
 int bcp_solver_kind(const bcp_env* env) {
   if (!env) return fail("bcp_solver_kind: null handle");
-  if (env->f64() || !env->use_split || !env->split.recs) return BCP_SOLVER_ONE_LAUNCH;
-  return (env->split.cont && bcp::split_uses_lambda(env->p32)) ? BCP_SOLVER_SPLIT_IMPULSE : BCP_SOLVER_SPLIT_ROW;
+  if (env->f64() || !env->use_split || !env->recs) return BCP_SOLVER_ONE_LAUNCH;
+  return env->use_lam ? BCP_SOLVER_SPLIT_IMPULSE : BCP_SOLVER_SPLIT_ROW;
 }
 
 int bcp_profile_begin(bcp_env* h) {
@@ -482,13 +574,13 @@ int bcp_profile_end(bcp_env* h, double* out4) {
 
 int bcp_last_solve_info(bcp_env* h, int32_t* host_out, size_t n_ints, void* stream) {
   if (!h || !host_out) return fail("bcp_last_solve_info: null argument");
-  if (h->f64() || !h->use_split || !h->split.recs) return fail("bcp_last_solve_info: the handle does not run the split pipeline");
+  if (h->f64() || !h->use_split || !h->recs) return fail("bcp_last_solve_info: the handle does not run the split pipeline");
   if (n_ints != 4 * (size_t)h->cfg.num_envs) return fail("bcp_last_solve_info: n_ints must be 4 * num_envs");
   DeviceGuard g(h->cfg.device_ordinal);
   cudaStream_t s = (cudaStream_t)stream;
   // the first four words of every record: three contact counts and the iteration count (bit patterns of ints)
   const size_t pitch = bcp::split_record_words(h->p32) * sizeof(float);
-  CK(cudaMemcpy2DAsync(host_out, 4 * sizeof(int32_t), h->split.recs, pitch, 4 * sizeof(int32_t), (size_t)h->cfg.num_envs,
+  CK(cudaMemcpy2DAsync(host_out, 4 * sizeof(int32_t), h->recs, pitch, 4 * sizeof(int32_t), (size_t)h->cfg.num_envs,
                        cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   return 0;
@@ -497,28 +589,28 @@ int bcp_last_solve_info(bcp_env* h, int32_t* host_out, size_t n_ints, void* stre
 
 int bcp_solve_trace_enable(bcp_env* h, int on) {
   if (!h) return fail("bcp_solve_trace_enable: null handle");
-  if (h->f64() || !h->use_split || !h->split.recs) return fail("bcp_solve_trace_enable: the handle does not run the split pipeline");
+  if (h->f64() || !h->use_split || !h->recs) return fail("bcp_solve_trace_enable: the handle does not run the split pipeline");
   DeviceGuard g(h->cfg.device_ordinal);
-  if (on && !h->split.trace) {
+  if (on && !h->trace) {
     const size_t bytes = (size_t)h->cfg.action_repeats * h->cfg.steps_per_repeat * h->cfg.num_envs * 4 * sizeof(int);
-    CK(cudaMalloc((void**)&h->split.trace, bytes));
-    CK(cudaMemset(h->split.trace, 0, bytes));
-  } else if (!on && h->split.trace) {
+    CK(cudaMalloc((void**)&h->trace, bytes));
+    CK(cudaMemset(h->trace, 0, bytes));
+  } else if (!on && h->trace) {
     CK(cudaDeviceSynchronize());
-    CK(cudaFree(h->split.trace));
-    h->split.trace = nullptr;
+    CK(cudaFree(h->trace));
+    h->trace = nullptr;
   }
   return 0;
 }
 
 int bcp_solve_trace_read(bcp_env* h, int32_t* host_out, size_t n_ints, void* stream) {
   if (!h || !host_out) return fail("bcp_solve_trace_read: null argument");
-  if (!h->split.trace) return fail("bcp_solve_trace_read: tracing is not enabled on this handle");
+  if (!h->trace) return fail("bcp_solve_trace_read: tracing is not enabled on this handle");
   const size_t need = (size_t)h->cfg.action_repeats * h->cfg.steps_per_repeat * h->cfg.num_envs * 4;
   if (n_ints != need) return fail("bcp_solve_trace_read: n_ints must be 4 * R * S * num_envs");
   DeviceGuard g(h->cfg.device_ordinal);
   cudaStream_t s = (cudaStream_t)stream;
-  CK(cudaMemcpyAsync(host_out, h->split.trace, need * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
+  CK(cudaMemcpyAsync(host_out, h->trace, need * sizeof(int32_t), cudaMemcpyDeviceToHost, s));
   CK(cudaStreamSynchronize(s));
   return 0;
 }

@@ -177,7 +177,18 @@ BCP_HD_NOINLINE int box_box(const T p1[3], const T* R1, const T h1[3], const T p
   }
   rect[0] = Sa[code1];
   rect[1] = Sa[code2];
-  const int n = intersect_rect_quad(rect, quad, ret, buffer);
+  // The incident quad strictly inside the reference rectangle - a foot on the cart, a body well inside the ground
+  // plate - is the common case, and there intersectRectQuad2 is the identity: each of its four passes finds every point
+  // on the inner side (sign * p[dir] < h[dir] for both signs <=> |p[dir]| < h[dir]), copies it, and sees no crossing.
+  // Same four points in the same order, without the clipper.
+  bool inside = true;
+  for (int i = 0; i < 4; ++i) inside = inside && (babs(quad[2 * i]) < rect[0]) && (babs(quad[2 * i + 1]) < rect[1]);
+  int n = 4;
+  if (inside) {
+    for (int i = 0; i < 8; ++i) ret[i] = quad[i];
+  } else {
+    n = intersect_rect_quad(rect, quad, ret, buffer);
+  }
   if (n < 1) return 0;
   const T det1 = T(1.0) / (m11 * m22 - m12 * m21);
   m11 *= det1; m12 *= det1; m21 *= det1; m22 *= det1;

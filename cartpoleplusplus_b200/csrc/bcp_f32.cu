@@ -63,7 +63,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   // (measured on B200: +6..7 % env-steps/s at 32 768 and 65 536 envs, equal at 131 072); beyond
   // that the phase is issue-bound and building the matrices costs more than it saves (-3 % at
   // 262 144, -8 % at 1 M).  BCP_LAMBDA=1 / 0 forces it on / off.
-  const int use_lam = (split_uses_lambda(P) && b.cont) ? 1 : 0;
+  const int use_lam = ((b.lam < 0 ? split_uses_lambda(P) : b.lam != 0) && b.cont) ? 1 : 0;
   static int handoff = -1;
   if (handoff < 0) {
     const char* he = getenv("BCP_HANDOFF");
@@ -148,7 +148,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
       }
       if (launches) ++*launches;
       if (b.trace)  // instrumentation of the parity tests: what every env's solve of substep k did
-        cudaMemcpy2DAsync(b.trace + (size_t)k * N * 4, 4 * sizeof(int), b.recs, (size_t)rec_words * sizeof(float), 4 * sizeof(int), (size_t)N,
+        cudaMemcpy2DAsync(b.trace + (size_t)k * (b.trace_stride > 0 ? b.trace_stride : N) * 4, 4 * sizeof(int), b.recs, (size_t)rec_words * sizeof(float), 4 * sizeof(int), (size_t)N,
                           cudaMemcpyDeviceToDevice, s);
       mark();
     }

@@ -49,6 +49,8 @@ struct SplitBuffers {
   // optional (bcp_solve_trace_enable): [R*S][num_envs][4] ints, the first four words of every solve record
   // (three contact counts, PGS iterations) copied out after the solve phase of each substep of a call
   int* trace;
+  int trace_stride;  // envs per substep block of `trace` (the handle's env count: a cohort's buffers are views)
+  int lam;           // impulse-space solve phase on the main queue: decided once per handle (-1: from this view's size)
 };
 size_t split_cont_words(const Params<float>& P);
 bool split_uses_lambda(const Params<float>& P);  // impulse-space solve phase for this configuration / batch size?
