@@ -56,7 +56,7 @@ struct bcp_env {
   struct Cohort {
     int base = 0, n = 0;
     bcp::Params<float> P;
-    bcp::SplitBuffers b = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, -1};
+    bcp::SplitBuffers b = {nullptr, nullptr, nullptr, {nullptr, nullptr}, {nullptr, nullptr}, -1, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, -1, 0};
     cudaStream_t stream = nullptr;   // cohort 0 runs on the caller's stream
     cudaEvent_t ev_done = nullptr;
     std::vector<cudaEvent_t> ev_prep;  // bcp_step_host: after the k-th k_prep of the call
@@ -67,6 +67,22 @@ struct bcp_env {
   int* trace = nullptr;    // bcp_solve_trace_*: [R*S][N][4]
   int use_split = 0;
   int use_lam = 0;
+  // CUDA graphs of the plain bcp_step (no hook, no profiling, no trace): one per (output pointers, visiting-order parity).
+  // The actions are copied into act_buf first, so the caller's action pointer is not part of the key.
+  struct StepGraph {
+    float* obs; float* reward; uint8_t* done; uint8_t* reason; int parity; cudaStream_t stream;
+    cudaGraphExec_t exec; int launches;
+  };
+  std::vector<StepGraph> graphs;
+  struct HostGraph {
+    const void* act; float* obs; float* reward; uint8_t* done; uint8_t* reason; int parity;
+    cudaGraphExec_t exec; int launches;
+  };
+  std::vector<HostGraph> host_graphs;
+  int use_graph = 1;
+  void* act_buf = nullptr;
+  cudaStream_t gstream = nullptr;      // graphs are captured and launched here (the caller's stream may be the legacy default
+  cudaEvent_t ev_gin = nullptr, ev_gout = nullptr;  // stream, which cannot capture), forked from / joined into the caller's
   // bcp_step_host's hook into the cohorts' launch sequences
   struct HookArg { bcp_env* h; int cohort; };
   void (*split_hook)(void* ctx, int k, cudaStream_t s) = nullptr;
@@ -206,6 +222,12 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
         }
       }
       if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming);
+      A(&h->act_buf, N * 2 * sizeof(float));
+      const char* gv = getenv("BCP_GRAPH");
+      h->use_graph = gv ? atoi(gv) != 0 : 1;
+      if (err == cudaSuccess) err = cudaStreamCreateWithFlags(&h->gstream, cudaStreamNonBlocking);
+      if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_gin, cudaEventDisableTiming);
+      if (err == cudaSuccess) err = cudaEventCreateWithFlags(&h->ev_gout, cudaEventDisableTiming);
     }
   }
   if (err != cudaSuccess) {
@@ -233,6 +255,10 @@ int bcp_destroy(bcp_env* h) {
     if (co.ev_done) cudaEventDestroy(co.ev_done);
     for (cudaEvent_t e : co.ev_prep) cudaEventDestroy(e);
   }
+  for (bcp_env::StepGraph& g : h->graphs) cudaGraphExecDestroy(g.exec);
+  for (bcp_env::HostGraph& g : h->host_graphs) cudaGraphExecDestroy(g.exec);
+  cudaFree(h->act_buf);
+  if (h->gstream) { cudaStreamDestroy(h->gstream); cudaEventDestroy(h->ev_gin); cudaEventDestroy(h->ev_gout); }
   if (h->ev_fork) cudaEventDestroy(h->ev_fork);
   cudaFree(h->trace);
   cudaFree(h->recs);
@@ -256,6 +282,42 @@ int bcp_reset(bcp_env* h, const uint8_t* mask, float* obs_out, void* stream) {
   return 0;
 }
 
+}  // extern "C"
+
+// one call of every cohort, enqueued on `s` and the cohorts' own streams (forked from and joined back into `s`)
+static int enqueue_split(bcp_env* h, const void* actions, float* obs_out, float* reward_out, uint8_t* done_out, uint8_t* reason_out,
+                         cudaStream_t s, int* launches) {
+  const int width = 14 * h->cfg.action_repeats;
+  const size_t abytes = h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float);
+  // while the kernels are being bracketed by events (bcp_profile_begin) the cohorts run one after the other on the
+  // caller's stream, so that a kernel's time is its own
+  const bool fork = h->cohorts.size() > 1 && !h->profiling;
+  if (fork) CK(cudaEventRecord(h->ev_fork, s));
+  for (size_t c = 0; c < h->cohorts.size(); ++c) {
+    bcp_env::Cohort& co = h->cohorts[c];
+    cudaStream_t cs = (fork && c > 0) ? co.stream : s;
+    if (fork && c > 0) CK(cudaStreamWaitEvent(cs, h->ev_fork, 0));
+    const size_t b = (size_t)co.base;
+    const size_t ev0 = h->prof_events.size();
+    co.b.trace = h->trace ? h->trace + b * 4 : nullptr;
+    co.b.after_prep = h->split_hook;
+    co.b.hook_ctx = h->split_hook ? &h->hook_args[c] : nullptr;
+    CK(bcp::launch_step_split(co.P, (float*)h->fdata + b * bcp::NF, h->idata + b * bcp::NI, co.b,
+                              static_cast<const char*>(actions) + b * abytes, obs_out ? obs_out + b * width : nullptr,
+                              reward_out ? reward_out + b : nullptr, done_out ? done_out + b : nullptr,
+                              reason_out ? reason_out + b : nullptr, h->stats(), cs, launches,
+                              h->profiling ? &h->prof_events : nullptr));
+    if (h->profiling) h->prof_calls.push_back((int)(h->prof_events.size() - ev0));
+    if (fork && c > 0) {
+      CK(cudaEventRecord(co.ev_done, cs));
+      CK(cudaStreamWaitEvent(s, co.ev_done, 0));
+    }
+  }
+  return 0;
+}
+
+extern "C" {
+
 int bcp_step(bcp_env* h, const void* actions, float* obs_out, float* reward_out, uint8_t* done_out,
              uint8_t* reason_out, void* stream) {
   if (!h) return fail("bcp_step: null handle");
@@ -263,33 +325,52 @@ int bcp_step(bcp_env* h, const void* actions, float* obs_out, float* reward_out,
   DeviceGuard g(h->cfg.device_ordinal);
   cudaStream_t s = (cudaStream_t)stream;
   if (!h->f64() && h->use_split) {
-    int n = 0;
-    const int width = 14 * h->cfg.action_repeats;
-    const size_t abytes = h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float);
-    // while the kernels are being bracketed by events (bcp_profile_begin) the cohorts run one after the other on the
-    // caller's stream, so that a kernel's time is its own
-    const bool fork = h->cohorts.size() > 1 && !h->profiling;
-    if (fork) CK(cudaEventRecord(h->ev_fork, s));
-    for (size_t c = 0; c < h->cohorts.size(); ++c) {
-      bcp_env::Cohort& co = h->cohorts[c];
-      cudaStream_t cs = (fork && c > 0) ? co.stream : s;
-      if (fork && c > 0) CK(cudaStreamWaitEvent(cs, h->ev_fork, 0));
-      const size_t b = (size_t)co.base;
-      const size_t ev0 = h->prof_events.size();
-      co.b.trace = h->trace ? h->trace + b * 4 : nullptr;
-      co.b.after_prep = h->split_hook;
-      co.b.hook_ctx = h->split_hook ? &h->hook_args[c] : nullptr;
-      CK(bcp::launch_step_split(co.P, (float*)h->fdata + b * bcp::NF, h->idata + b * bcp::NI, co.b,
-                                static_cast<const char*>(actions) + b * abytes, obs_out ? obs_out + b * width : nullptr,
-                                reward_out ? reward_out + b : nullptr, done_out ? done_out + b : nullptr,
-                                reason_out ? reason_out + b : nullptr, h->stats(), cs, &n,
-                                h->profiling ? &h->prof_events : nullptr));
-      if (h->profiling) h->prof_calls.push_back((int)(h->prof_events.size() - ev0));
-      if (fork && c > 0) {
-        CK(cudaEventRecord(co.ev_done, cs));
-        CK(cudaStreamWaitEvent(s, co.ev_done, 0));
+    // Steady state: the whole call - every cohort's memsets and kernels, the forks to the cohort and side streams and their
+    // joins - is one CUDA graph launch (the host then spends ~10 us per env.step instead of one launch call per kernel).
+    // Captured the first time a (outputs, stream, visiting-order parity) combination is seen after the handle's first call.
+    const bool plain = h->use_graph && !h->profiling && !h->trace && !h->split_hook && h->cohorts[0].b.cur >= 0 && h->cohorts[0].b.side_ready;
+    if (plain) {
+      const size_t abytes = (size_t)h->cfg.num_envs * (h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float));
+      const int parity = h->cohorts[0].b.cur;
+      bcp_env::StepGraph* g = nullptr;
+      for (bcp_env::StepGraph& c : h->graphs)
+        if (c.obs == obs_out && c.reward == reward_out && c.done == done_out && c.reason == reason_out && c.parity == parity) g = &c;
+      if (!g && h->graphs.size() < 16) {
+        cudaGraph_t graph = nullptr;
+        int n = 0;
+        cudaError_t e = cudaStreamBeginCapture(h->gstream, cudaStreamCaptureModeThreadLocal);
+        int rc = 0;
+        if (e == cudaSuccess) {
+          rc = enqueue_split(h, h->act_buf, obs_out, reward_out, done_out, reason_out, h->gstream, &n);
+          e = cudaStreamEndCapture(h->gstream, &graph);
+        }
+        cudaGraphExec_t exec = nullptr;
+        if (e == cudaSuccess && rc == 0 && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+        if (graph) cudaGraphDestroy(graph);
+        if (e != cudaSuccess || rc != 0 || !exec) {   // no graphs on this handle from now on; the direct path below still works
+          cudaGetLastError();
+          h->use_graph = 0;
+          for (bcp_env::Cohort& co : h->cohorts) co.b.cur = parity;   // the captured enqueue flipped it
+        } else {
+          for (bcp_env::Cohort& co : h->cohorts) co.b.cur = parity;   // the capture ran the host code once: undo its flip
+          h->graphs.push_back(bcp_env::StepGraph{obs_out, reward_out, done_out, reason_out, parity, h->gstream, exec, n});
+          g = &h->graphs.back();
+        }
+      }
+      if (g) {
+        CK(cudaMemcpyAsync(h->act_buf, actions, abytes, cudaMemcpyDeviceToDevice, s));
+        CK(cudaEventRecord(h->ev_gin, s));
+        CK(cudaStreamWaitEvent(h->gstream, h->ev_gin, 0));
+        CK(cudaGraphLaunch(g->exec, h->gstream));
+        CK(cudaEventRecord(h->ev_gout, h->gstream));
+        CK(cudaStreamWaitEvent(s, h->ev_gout, 0));
+        for (bcp_env::Cohort& co : h->cohorts) co.b.cur = 1 - parity;
+        h->launches += g->launches;
+        return 0;
       }
     }
+    int n = 0;
+    if (enqueue_split(h, actions, obs_out, reward_out, done_out, reason_out, s, &n)) return -1;
     h->launches += n;
     return 0;
   }
@@ -346,6 +427,58 @@ void host_step_hook(void* ctx, int k, cudaStream_t s) {
 }
 }  // namespace
 
+}  // extern "C"
+
+// the host-buffer call, enqueued on `s` (and the copy / cohort / side streams forked from it and joined back)
+static int host_step_enqueue(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_reward, uint8_t* h_done, uint8_t* h_reason,
+                             cudaStream_t s) {
+  const size_t n = (size_t)h->cfg.num_envs, R = (size_t)h->cfg.action_repeats;
+  const size_t ob = n * R * 14 * sizeof(float), rb = n * sizeof(float);
+  const size_t ab = n * (h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float));
+  float* d_obs = reinterpret_cast<float*>(h->hs.d_out);
+  float* d_rew = reinterpret_cast<float*>(h->hs.d_out + ob);
+  uint8_t* d_done = h->hs.d_out + ob + rb;
+  uint8_t* d_reason = d_done + n;
+  const bool split = !h->f64() && h->use_split;
+  if (split) {  // the first kernel of a split call (collision pass and rows of substep 0) does not depend on the actions
+    CK(cudaEventRecord(h->hs.ev_ready, s));
+    CK(cudaStreamWaitEvent(h->hs.copy, h->hs.ev_ready, 0));  // whatever read d_act before is done
+    CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, h->hs.copy));
+    CK(cudaEventRecord(h->hs.ev_h2d, h->hs.copy));
+    h->hs.h2d_pending = true;
+  } else {
+    CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, s));
+  }
+  h->hs.h_obs = h_obs_rm;
+  h->hs.fired = false;
+  if (split) {
+    h->hook_args.resize(h->cohorts.size());
+    for (size_t c = 0; c < h->cohorts.size(); ++c) h->hook_args[c] = bcp_env::HookArg{h, (int)c};
+    h->split_hook = host_step_hook;
+  }
+  const int rc = bcp_step(h, h->hs.d_act, d_obs, d_rew, d_done, d_reason, (void*)s);
+  h->split_hook = nullptr;
+  if (h->hs.h2d_pending) {  // the call failed before its first kernel
+    cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);
+    h->hs.h2d_pending = false;
+  }
+  if (rc) return rc;
+  // the repeats that did not leave during the call (all of them on the one-launch pipeline)
+  for (int r = h->hs.fired ? (int)R - 1 : 0; r < (int)R; ++r) pack_and_copy(h, r, s);
+  if (reinterpret_cast<uint8_t*>(h_reward) + rb == h_done && h_done + n == h_reason) {
+    CK(cudaMemcpyAsync(h_reward, d_rew, rb + 2 * n, cudaMemcpyDeviceToHost, s));  // one transfer when the caller's buffers are adjacent
+  } else {
+    CK(cudaMemcpyAsync(h_reward, d_rew, rb, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h_done, d_done, n, cudaMemcpyDeviceToHost, s));
+    CK(cudaMemcpyAsync(h_reason, d_reason, n, cudaMemcpyDeviceToHost, s));
+  }
+  if (h->hs.fired) CK(cudaStreamWaitEvent(s, h->hs.ev_copied, 0));  // a sync on `stream` covers the early slabs too
+  CK(cudaGetLastError());
+  return 0;
+}
+
+extern "C" {
+
 int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_reward, uint8_t* h_done, uint8_t* h_reason,
                   void* stream) {
   if (!h) return fail("bcp_step_host: null handle");
@@ -371,46 +504,50 @@ int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_r
     CK(cudaEventCreateWithFlags(&h->hs.ev_copied, cudaEventDisableTiming));
     CK(cudaEventCreateWithFlags(&h->hs.ev_h2d, cudaEventDisableTiming));
   }
-  float* d_obs = reinterpret_cast<float*>(h->hs.d_out);
-  float* d_rew = reinterpret_cast<float*>(h->hs.d_out + ob);
-  uint8_t* d_done = h->hs.d_out + ob + rb;
-  uint8_t* d_reason = d_done + n;
-  const bool split = !h->f64() && h->use_split;
-  if (split) {  // the first kernel of a split call (collision pass and rows of substep 0) does not depend on the actions
-    CK(cudaEventRecord(h->hs.ev_ready, s));
-    CK(cudaStreamWaitEvent(h->hs.copy, h->hs.ev_ready, 0));  // whatever read d_act before is done
-    CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, h->hs.copy));
-    CK(cudaEventRecord(h->hs.ev_h2d, h->hs.copy));
-    h->hs.h2d_pending = true;
-  } else {
-    CK(cudaMemcpyAsync(h->hs.d_act, h_actions, ab, cudaMemcpyHostToDevice, s));
+  // Steady state on the split pipeline: the whole host call - H2D of the actions, every cohort's kernels, the slab packs
+  // and the D2H copies into the caller's (pinned, pointer-stable) buffers - is one CUDA graph per (buffers, parity).
+  const bool can_graph = h->use_graph && !h->f64() && h->use_split && !h->profiling && !h->trace && h->cohorts[0].b.cur >= 0 &&
+                         h->cohorts[0].b.side_ready;
+  if (can_graph) {
+    const int parity = h->cohorts[0].b.cur;
+    bcp_env::HostGraph* hg = nullptr;
+    for (bcp_env::HostGraph& c : h->host_graphs)
+      if (c.act == h_actions && c.obs == h_obs_rm && c.reward == h_reward && c.done == h_done && c.reason == h_reason && c.parity == parity) hg = &c;
+    if (!hg && h->host_graphs.size() < 16) {
+      cudaGraph_t graph = nullptr;
+      const int64_t l0 = h->launches;
+      cudaError_t e = cudaStreamBeginCapture(h->gstream, cudaStreamCaptureModeThreadLocal);
+      int rc = 0;
+      if (e == cudaSuccess) {
+        rc = host_step_enqueue(h, h_actions, h_obs_rm, h_reward, h_done, h_reason, h->gstream);
+        e = cudaStreamEndCapture(h->gstream, &graph);
+      }
+      const int nl = (int)(h->launches - l0);
+      h->launches = l0;
+      cudaGraphExec_t exec = nullptr;
+      if (e == cudaSuccess && rc == 0 && graph) e = cudaGraphInstantiate(&exec, graph, 0);
+      if (graph) cudaGraphDestroy(graph);
+      for (bcp_env::Cohort& co : h->cohorts) co.b.cur = parity;   // the captured enqueue flipped it
+      if (e != cudaSuccess || rc != 0 || !exec) {
+        cudaGetLastError();
+        h->use_graph = 0;
+      } else {
+        h->host_graphs.push_back(bcp_env::HostGraph{h_actions, h_obs_rm, h_reward, h_done, h_reason, parity, exec, nl});
+        hg = &h->host_graphs.back();
+      }
+    }
+    if (hg) {
+      CK(cudaEventRecord(h->ev_gin, s));
+      CK(cudaStreamWaitEvent(h->gstream, h->ev_gin, 0));
+      CK(cudaGraphLaunch(hg->exec, h->gstream));
+      CK(cudaEventRecord(h->ev_gout, h->gstream));
+      CK(cudaStreamWaitEvent(s, h->ev_gout, 0));
+      for (bcp_env::Cohort& co : h->cohorts) co.b.cur = 1 - parity;
+      h->launches += hg->launches;
+      return 0;
+    }
   }
-  h->hs.h_obs = h_obs_rm;
-  h->hs.fired = false;
-  if (split) {
-    h->hook_args.resize(h->cohorts.size());
-    for (size_t c = 0; c < h->cohorts.size(); ++c) h->hook_args[c] = bcp_env::HookArg{h, (int)c};
-    h->split_hook = host_step_hook;
-  }
-  const int rc = bcp_step(h, h->hs.d_act, d_obs, d_rew, d_done, d_reason, stream);
-  h->split_hook = nullptr;
-  if (h->hs.h2d_pending) {  // the call failed before its first kernel
-    cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);
-    h->hs.h2d_pending = false;
-  }
-  if (rc) return rc;
-  // the repeats that did not leave during the call (all of them on the one-launch pipeline)
-  for (int r = h->hs.fired ? (int)R - 1 : 0; r < (int)R; ++r) pack_and_copy(h, r, s);
-  if (reinterpret_cast<uint8_t*>(h_reward) + rb == h_done && h_done + n == h_reason) {
-    CK(cudaMemcpyAsync(h_reward, d_rew, rb + 2 * n, cudaMemcpyDeviceToHost, s));  // one transfer when the caller's buffers are adjacent
-  } else {
-    CK(cudaMemcpyAsync(h_reward, d_rew, rb, cudaMemcpyDeviceToHost, s));
-    CK(cudaMemcpyAsync(h_done, d_done, n, cudaMemcpyDeviceToHost, s));
-    CK(cudaMemcpyAsync(h_reason, d_reason, n, cudaMemcpyDeviceToHost, s));
-  }
-  if (h->hs.fired) CK(cudaStreamWaitEvent(s, h->hs.ev_copied, 0));  // a sync on `stream` covers the early slabs too
-  CK(cudaGetLastError());
-  return 0;
+  return host_step_enqueue(h, h_actions, h_obs_rm, h_reward, h_done, h_reason, s);
 }
 
 int bcp_step_host_finish(bcp_env* h, float* h_obs_rm, const uint8_t* h_reason, void* stream) {

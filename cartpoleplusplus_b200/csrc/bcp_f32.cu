@@ -154,6 +154,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
     }
   }
   b.cur = nxt;
+  b.side_ready = 1;
   return cudaGetLastError();
 }
 cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers& b, const void* actions, float* obs,

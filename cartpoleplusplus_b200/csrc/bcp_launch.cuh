@@ -51,6 +51,7 @@ struct SplitBuffers {
   int* trace;
   int trace_stride;  // envs per substep block of `trace` (the handle's env count: a cohort's buffers are views)
   int lam;           // impulse-space solve phase on the main queue: decided once per handle (-1: from this view's size)
+  int side_ready;    // the lazily created side stream / kernel attributes exist (or are not needed): the call can be captured
 };
 size_t split_cont_words(const Params<float>& P);
 bool split_uses_lambda(const Params<float>& P);  // impulse-space solve phase for this configuration / batch size?

@@ -186,21 +186,9 @@ class BatchedBulletCartpole:
         env.reason are those of the last step() and are NOT updated by this call (use the returned host tensors).
         auto_reset=True (reset(mask=done) after the step, so that the next observation of a finished
         env is its reset observation) takes the plain path: step, one D2H, reset."""
-        n, R = self.num_envs, self.repeats
         if self._renderer is not None:
             raise _lib.BcpError("step_host moves the low-dimensional observation; with --use-raw-pixels use step()")
-        if not hasattr(self, "_h_out"):
-            ob, rb = self.obs.numel() * 4, n * 4
-            self._h_out = torch.empty(self._out.numel(), dtype=torch.uint8).pin_memory()
-            self._h_obs = self._h_out[:ob].view(torch.float32).view(self.obs.shape)
-            self._h_obs_rm = self._h_out[:ob].view(torch.float32).view(R, n, 2, 7)  # the same bytes, repeat-major
-            self._h_reward = self._h_out[ob:ob + rb].view(torch.float32)
-            self._h_done = self._h_out[ob + rb:ob + rb + n]
-            self._h_reason = self._h_out[ob + rb + n:]
-            adt = torch.int32 if self.discrete_actions else torch.float32
-            ashape = (n,) if self.discrete_actions else (n, 2)
-            self._d_act = torch.empty(ashape, dtype=adt, device=self.device)
-            self._h_act = torch.empty(ashape, dtype=adt).pin_memory()
+        self._host_buffers()
         if auto_reset:
             self._d_act.copy_(actions_host.reshape(self._d_act.shape), non_blocking=True)
             self.step(self._d_act, copy=False)
@@ -208,22 +196,65 @@ class BatchedBulletCartpole:
             self.reset(mask=self.done, copy=False)
             torch.cuda.current_stream(self.device).synchronize()
             return self._h_obs, self._h_reward, self._h_done, {"done_reason": self._h_reason}
+        self.step_host_begin(actions_host)
+        return self.step_host_end()
+
+    def step_host_begin(self, actions_host: torch.Tensor):
+        """First half of step_host: enqueues the H2D copy of the actions, the step and the D2H copies of its outputs on the
+        env's own host-step stream and returns at once.  A host loop that drives two envs alternately
+        (`a.step_host_begin(x); b.step_host_end(); b.step_host_begin(y); a.step_host_end(); ...`) has one env's outputs
+        crossing PCIe - and being read on the host - while the other env steps."""
         if not self._was_reset:
             raise _lib.BcpError("step() before reset()")
+        if self._renderer is not None:
+            raise _lib.BcpError("step_host moves the low-dimensional observation; with --use-raw-pixels use step()")
+        self._host_buffers()
+        if getattr(self, "_host_pending", False):
+            raise _lib.BcpError("step_host_begin() twice without step_host_end()")
         a = actions_host
         if not (type(a) is torch.Tensor and a.dtype == self._h_act.dtype and a.is_pinned() and a.is_contiguous()
                 and a.numel() == self._h_act.numel()):
             self._h_act.copy_(torch.as_tensor(actions_host).reshape(self._h_act.shape))
             a = self._h_act
         vp = ctypes.c_void_p
-        st = self._stream()
+        if self._host_stream is None:  # ordered after whatever the caller's stream did to the env (reset, set_state)
+            self._host_stream = torch.cuda.Stream(device=self.device)
+        self._host_stream.wait_stream(torch.cuda.current_stream(self.device))
+        st = vp(self._host_stream.cuda_stream)
         _lib.check(self._lib.bcp_step_host(self._h, vp(a.data_ptr()), vp(self._h_obs_rm.data_ptr()), vp(self._h_reward.data_ptr()),
                                            vp(self._h_done.data_ptr()), vp(self._h_reason.data_ptr()), st), self._lib)
-        _lib.check(self._lib.bcp_step_host_finish(self._h, vp(self._h_obs_rm.data_ptr()), vp(self._h_reason.data_ptr()), st), self._lib)
+        self._host_actions, self._host_pending = a, True
+
+    def step_host_end(self):
+        """Second half of step_host: waits for the call begun by step_host_begin and returns its host tensors."""
+        if not getattr(self, "_host_pending", False):
+            raise _lib.BcpError("step_host_end() without step_host_begin()")
+        vp = ctypes.c_void_p
+        _lib.check(self._lib.bcp_step_host_finish(self._h, vp(self._h_obs_rm.data_ptr()), vp(self._h_reason.data_ptr()),
+                                                  vp(self._host_stream.cuda_stream)), self._lib)
+        self._host_pending = False
+        torch.cuda.current_stream(self.device).wait_stream(self._host_stream)
         if self.event_log is not None:
-            self.event_log.observe(a.numpy().reshape(n, -1), self._h_obs_rm.permute(1, 0, 2, 3).numpy(), self._h_reward.numpy(), self._h_done.numpy(),
-                                   self._h_reason.numpy())
+            self.event_log.observe(self._host_actions.numpy().reshape(self.num_envs, -1), self._h_obs_rm.permute(1, 0, 2, 3).numpy(),
+                                   self._h_reward.numpy(), self._h_done.numpy(), self._h_reason.numpy())
         return self._h_obs_rm.permute(1, 0, 2, 3), self._h_reward, self._h_done, {"done_reason": self._h_reason}
+
+    def _host_buffers(self):
+        if hasattr(self, "_h_out"):
+            return
+        n, R = self.num_envs, self.repeats
+        ob, rb = self.obs.numel() * 4, n * 4
+        self._h_out = torch.empty(self._out.numel(), dtype=torch.uint8).pin_memory()
+        self._h_obs = self._h_out[:ob].view(torch.float32).view(self.obs.shape)
+        self._h_obs_rm = self._h_out[:ob].view(torch.float32).view(R, n, 2, 7)  # the same bytes, repeat-major
+        self._h_reward = self._h_out[ob:ob + rb].view(torch.float32)
+        self._h_done = self._h_out[ob + rb:ob + rb + n]
+        self._h_reason = self._h_out[ob + rb + n:]
+        adt = torch.int32 if self.discrete_actions else torch.float32
+        ashape = (n,) if self.discrete_actions else (n, 2)
+        self._d_act = torch.empty(ashape, dtype=adt, device=self.device)
+        self._h_act = torch.empty(ashape, dtype=adt).pin_memory()
+        self._host_stream = None
 
     @property
     def h2d_bytes_per_step(self) -> int:
