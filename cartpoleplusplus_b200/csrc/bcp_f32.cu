@@ -11,12 +11,12 @@ size_t split_cont_words(const Params<float>& P) { return (size_t)LAM_WORDS * (si
 size_t split_bins_words(const Params<float>& P) { return (size_t)N_BINS * (size_t)P.num_envs; }
 
 bool split_uses_lambda(const Params<float>& P) {
-  static int lam_env = -2;
-  if (lam_env == -2) {
-    const char* le = getenv("BCP_LAMBDA");
-    lam_env = le ? atoi(le) : -1;
-  }
-  const bool wanted = lam_env < 0 ? P.num_envs < 131072 : lam_env != 0;
+  // Impulse-space solve phase wherever its two regimes cover the configuration.  Round 1 switched to row space from
+  // 131 072 envs per handle (one pipeline: beyond a wave the matrix builds cost more than the shorter chain saves);
+  // with the handle run as cohorts of <= 65 536 envs the impulse-space phase wins at every size measured
+  // (131 072: 1.79e8 vs 1.56e8 env-steps/s, 262 144: 1.86e8 vs 1.63e8, 1 M: 1.91e8 vs 1.79e8).  BCP_LAMBDA=0 / 1 forces it.
+  const char* le = getenv("BCP_LAMBDA");
+  const bool wanted = le ? atoi(le) != 0 : true;
   return wanted && lam_config_ok(P);
 }
 

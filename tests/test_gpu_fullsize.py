@@ -53,10 +53,9 @@ def test_bookkeeping_identities_at_full_size(built):
 
 @pytest.mark.parametrize("N", [65536, 131072])
 def test_trajectories_do_not_depend_on_the_sharding(built, N):
-    """Whole batch vs two half-size handles with env_id_offset: bit for bit when whole and halves run the
-    same solver (the impulse-space solve phase serves handles below 131 072 envs, bcp_f32.cu), to fp32
-    rounding from identical states when they do not."""
-    exact = (N < 131072) == (N // 2 < 131072)
+    """Whole batch vs two half-size handles with env_id_offset: bit for bit - whole and halves run the same per-env
+    programs whatever the number of cohorts a handle is split into (bcp_abi.cu)."""
+    exact = True  # every size runs the impulse-space solve phase since the handle is run as cohorts (round 2)
     whole = _env(N, initial_force=55.0)
     halves = [_env(N // 2, offset=0, initial_force=55.0), _env(N // 2, offset=N // 2, initial_force=55.0)]
     def same(x, y):

@@ -21,8 +21,9 @@ pytestmark = pytest.mark.gpu
 CASES = {
     # BASELINE.json configs[2]: what bench.py times (split / impulse-space solve phase)
     "configs2_65536": dict(n=65536, discrete=False, ov=dict(initial_force=200.0, action_force=100.0, auto_reset="pipelined")),
-    # the same workload at the size where the row-space solve phase takes over
-    "configs2_131072_rowspace": dict(n=131072, discrete=False, ov=dict(initial_force=200.0, action_force=100.0, auto_reset="pipelined")),
+    # the same workload on the row-space solve phase (what configurations outside the impulse-space regimes run), two cohorts of 65 536
+    "configs2_131072_rowspace": dict(n=131072, discrete=False, env={"BCP_LAMBDA": "0"},
+                                     ov=dict(initial_force=200.0, action_force=100.0, auto_reset="pipelined")),
     # configs[1]-sized, discrete random actions with a push (the README's 4th protocol, README.md:90-92)
     "configs1_4096_discrete": dict(n=4096, discrete=True, ov=dict(initial_force=55.0, auto_reset="pipelined")),
     # upstream-style physics (pole stays on the cart, two-body friction rows live), one substep per call: north_star's
@@ -41,8 +42,13 @@ def test_timed_pipeline_against_fp64_oracle(built, name):
     from oracle import Oracle
     case = CASES[name]
     n = case["n"]
-    env = BatchedBulletCartpole(default_opts(**case["ov"]), discrete_actions=case["discrete"], num_envs=n, device=0, dtype="fp32", seed=17)
-    assert env.solver_kind == ("split/row-space" if n >= 131072 or case["ov"].get("cart_friction") else "split/impulse-space"), env.solver_kind
+    os.environ.update(case.get("env", {}))
+    try:
+        env = BatchedBulletCartpole(default_opts(**case["ov"]), discrete_actions=case["discrete"], num_envs=n, device=0, dtype="fp32", seed=17)
+    finally:
+        for k in case.get("env", {}):
+            os.environ.pop(k, None)
+    assert env.solver_kind == ("split/row-space" if case.get("env") or case["ov"].get("cart_friction") else "split/impulse-space"), env.solver_kind
     ora = Oracle(env.cfg, dtype="fp64")
     state = PU.stationary_mix(env, case.get("mix", 400))
     rng = np.random.default_rng(23)
