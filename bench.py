@@ -100,7 +100,8 @@ def cpu_rollout(args, n_envs, n_steps, warm_steps):
     return steps, resets, dt
 
 
-def cpu_baseline(args, budget_s=12.0):
+def cpu_baseline(args, budget_s=None):
+    budget_s = budget_s or args.cpu_budget
     cores = os.cpu_count() or 1
     n = 256 * cores
     steps, resets, dt = cpu_rollout(args, n, 8, 40)  # probe
@@ -111,6 +112,25 @@ def cpu_baseline(args, budget_s=12.0):
             "sample": f"{n} envs x {n_steps} env.steps (+{resets} resets of 130 substeps) of the same workload from its "
                       f"stationary phase mix, fp64 C oracle, OpenMP over {cores} threads; pybullet: unavailable on this box",
             "seconds": dt, "resets": resets}
+
+
+def secondary_workload(args):
+    """The workload where the pole is actually balanced on the cart (cart friction 1.0, R*S = 10, --initial-force=55: two-body
+    friction rows live, ~31 PGS iterations per substep), measured by this same script in a child process and reported BESIDE
+    the headline, never as it: SURVEY 8d asks for both workloads, each labelled."""
+    cmd = [sys.executable, os.path.abspath(__file__), "--cart-friction", "1.0", "--steps-per-repeat", "5", "--initial-force", "55",
+           "--steps", "10", "--warmup", "3", "--mix-calls", "60", "--envs", str(args.envs), "--no-secondary", "--cpu-budget", "6"]
+    try:
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        d = json.loads(r.stdout.strip().splitlines()[-1])
+    except Exception as e:
+        return {"unavailable": str(e)[:200]}
+    keep = ("value", "unit", "ms_per_step", "steps", "live_fraction", "substeps_per_s", "kernel_ms_per_step", "e2e", "cpu_baseline")
+    out = {k: d.get(k) for k in keep}
+    out["config"] = {k: d["config"].get(k) for k in ("envs_per_gpu", "action_repeats", "steps_per_repeat", "initial_force", "cart_friction", "pipeline")}
+    out["roofline"] = {k: d["roofline"].get(k) for k in ("bound", "whole_step_frac", "whole_step_achieved", "peak", "unit")}
+    out["census"] = d.get("census")
+    return out
 
 
 class ClockSampler(threading.Thread):
@@ -530,6 +550,8 @@ def run_ours(args):
             "note": "trajectories are keyed by global env id: deciles and hash must be identical for every N"}
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(args)
+    if world == 1 and not args.no_secondary and args.cart_friction is None:
+        out["upstream_style_workload"] = secondary_workload(args)
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -607,6 +629,8 @@ def main():
     ap.add_argument("--no-configs3", action="store_true", help="N >= 2: skip the configs[3] run (1 M envs sharded, deciles)")
     ap.add_argument("--configs3-envs", type=int, default=1048576)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the upstream-style (friction, R*S = 10) workload reported beside the headline")
+    ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work of the cpu_baseline sample")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     ensure_built()

@@ -57,10 +57,13 @@ template <typename V> BCP_HD V pick3(const V* a, int m) { return m == 0 ? a[0] :
 // handed to box_box by address (k_prep keeps them in the thread's shared-memory frame), while
 // the bodies and the impulse slots are only ever touched with compile-time offsets, so they
 // stay in registers.
-template <typename T> struct SetupFrame {  // what box_box reads and scribbles on
+template <typename T> struct SetupFrame {  // what box_box reads and scribbles on, and the manifold of the pair being worked on
   Posed<T> cbox, pbox;
-  T ws[kBoxWs];
+  T ws[kBoxWs];      // dBoxBox2's workspace; its <= 4 contacts come back in the first words; once they are in the manifold
+                     // the pair's world points (WorldPt x 4 = 24 words) take their place
+  Manifold<T> mf;    // in addressable memory: run-time indices (manifold_add_mem / manifold_refresh_mem), no 44 registers
 };
+static_assert(sizeof(WorldPt<float>) * 4 <= sizeof(float) * kBoxWs, "world points alias the narrowphase workspace");
 template <typename T> struct SetupCtx {
   FBody<T> cart, pole;
   T apn_all[N_SLOTS];
@@ -80,12 +83,13 @@ template <typename T> BCP_HD void setup_begin(const Params<T>& P, const Env<T>& 
   F.pbox = pb;
   for (int k = 0; k < N_SLOTS; ++k) C.apn_all[k] = T(0.0);
 }
+// `mf` is the frame's own manifold (F.mf): loaded by the caller, updated here in place
 template <typename T, bool FRICTION>
-BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, const Posed<T>& gbox, SetupFrame<T>& F, SetupCtx<T>& C,
+BCP_HD void setup_pair(const Params<T>& P, int m, const Posed<T>& gbox, SetupFrame<T>& F, SetupCtx<T>& C,
                        T* rec, const SolveLayout& L) {
+  Manifold<T>& mf = F.mf;
   const Posed<T>& Am = (m == BCP_PAIR_CART_POLE) ? F.cbox : gbox;
   const Posed<T>& Bm = (m == BCP_PAIR_GROUND_CART) ? F.cbox : F.pbox;
-  WorldPt<T> wp[4];
   const int nc = box_box(Am.x, Am.R, Am.h, Bm.x, Bm.R, Bm.h, F.ws);
   const Contact<T>* cs = box_contacts(F.ws);
   const Posed<T> A = Am, B = Bm;  // by value: read once, then registers
@@ -93,8 +97,9 @@ BCP_HD void setup_pair(const Params<T>& P, int m, Manifold<T>& mf, const Posed<T
   // is a slow, scoreboarded load
   const T brk = pick3(P.breaking, m);
   const int base = pick3(L.base, m), fbase = pick3(L.fbase, m), rpc = pick3(L.rpc, m);
-  for (int k = 0; k < nc; ++k) manifold_add(mf, A, B, cs[k], brk);
-  manifold_refresh(mf, A, B, brk, wp);
+  for (int k = 0; k < nc; ++k) manifold_add_mem(mf, A, B, cs[k], brk);
+  WorldPt<T>* wp = reinterpret_cast<WorldPt<T>*>(F.ws);  // the contacts are in the manifold now
+  manifold_refresh_mem(mf, A, B, brk, wp);
   T* rows = rec + REC_ROWS + base;
   T* frows = rec + REC_ROWS + (fbase >= 0 ? fbase : 0);
   if (m == BCP_PAIR_GROUND_CART) {
@@ -129,7 +134,11 @@ BCP_HD void split_setup(const Params<T>& P, Env<T>& st, T* rec, bool on) {
   ground_box(P, gbox);
   const SolveLayout L = solve_layout(P);
   setup_begin(P, st, F, C);
-  for (int m = 0; m < 3; ++m) setup_pair<T, FRICTION>(P, m, st.mani[m], gbox, F, C, rec, L);
+  for (int m = 0; m < 3; ++m) {
+    F.mf = st.mani[m];
+    setup_pair<T, FRICTION>(P, m, gbox, F, C, rec, L);
+    st.mani[m] = F.mf;
+  }
   setup_end(P, st, C, rec);
 }
 
@@ -383,7 +392,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     for (int m = 0; m < 3; ++m) {
       BCP_WARP_SYNC();
       if (on) {
-        Manifold<T> mf;
+        Manifold<T>& mf = F.mf;
         mf.count = st.mani[m].count;
         load_manifold<T>(f, e, m, mf);
         if (fin) {
@@ -391,7 +400,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
           for (int j = 0; j < 4; ++j)
             if (j < mf.count) mf.p[j].imp = fin_apn[slot_of_pair(m) + j];
         }
-        setup_pair<T, FRICTION>(P, m, mf, gbox, F, C, rec, L);
+        setup_pair<T, FRICTION>(P, m, gbox, F, C, rec, L);
         st.mani[m].count = mf.count;
         store_manifold<T>(f, e, m, mf);
       } else if (fin) {
@@ -479,6 +488,92 @@ __device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wai
 
 constexpr int kMaxPieces = 4;  // 16-byte pieces of a record one lane copies (records <= 512 words)
 
+// What k_solve and k_solve_lam share: a warp's slice of the queue, and the staged copy of the records it takes into the
+// lanes' shared-memory columns.
+//   init : this lane moves the 16-byte pieces lane, lane + 32, ... of every record its warp takes.  What block a piece
+//          lies in never changes, so it is worked out once: piece k is live iff
+//          pc_off[k] < count(pair pc_shift[k] / 8) * pc_per[k]   (header pieces: always).
+//   take : queue entries for the idle lanes (one atomic per warp per kFetchChunk entries; long-predicted solves come
+//          from the front of the queue, the rest from the back), then the whole warp issues the record -> column copies
+//          as 16-byte cp.async, zero-filled for the row slots an env does not use, and does not wait for them.
+//          Returns this lane's env (-1: none); `staged` = lanes whose copy is in flight.
+template <typename T> struct PoolFeed {
+  int pc_shift[kMaxPieces], pc_off[kMaxPieces], pc_per[kMaxPieces];
+  int w_next, w_end;  // the warp's slice of the queue (uniform)
+  int n_long, total, N, rec16;
+  bool exhausted;
+  __device__ __forceinline__ void init(const SolveLayout& L, int lane, int rec_words, const int* qc, int n_envs) {
+    N = n_envs;
+    n_long = qc[Q_LONG];
+    total = n_long + qc[Q_SHORT];
+    rec16 = (rec_words * (int)sizeof(T)) >> 4;
+    const int hdr16 = (REC_ROWS * (int)sizeof(T)) >> 4;
+#pragma unroll
+    for (int k = 0; k < kMaxPieces; ++k) {
+      const int i = lane + 32 * k;
+      pc_shift[k] = 0; pc_off[k] = (i < hdr16) ? -1 : 0x7fffffff; pc_per[k] = 0;  // header piece / outside every block
+#pragma unroll
+      for (int m = 0; m < 3; ++m) {
+        const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
+        const int lo = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4, per = (w * (int)sizeof(T)) >> 4;
+        if (i >= lo && i < lo + 4 * per) { pc_shift[k] = 8 * m; pc_off[k] = i - lo; pc_per[k] = per; }
+        if (L.fbase[m] >= 0) {
+          const int flo = ((REC_ROWS + L.fbase[m]) * (int)sizeof(T)) >> 4, fper = ((L.rpc[m] - 1) * w * (int)sizeof(T)) >> 4;
+          if (i >= flo && i < flo + 4 * fper) { pc_shift[k] = 8 * m; pc_off[k] = i - flo; pc_per[k] = fper; }
+        }
+      }
+    }
+    w_next = 0;
+    w_end = 0;
+    exhausted = total == 0;
+  }
+  __device__ __forceinline__ int take(unsigned idle, int lane, const int2* __restrict__ queue, int* __restrict__ qc, const T* __restrict__ recs,
+                                      int rec_words, T* smem, int warp_base, int col_stride, unsigned& staged) {
+    const unsigned FULL = 0xffffffffu, lt = (1u << lane) - 1;
+    unsigned need = idle;
+    int idx = -1;
+    while (need && !exhausted) {
+      const int avail = w_end - w_next;
+      const int rank = __popc(need & lt);
+      const bool mine = ((need >> lane) & 1u) && rank < avail;
+      if (mine) idx = w_next + rank;
+      const unsigned got = __ballot_sync(FULL, mine);
+      need &= ~got;
+      w_next += __popc(got);
+      if (!need) break;
+      int b = 0;
+      if (lane == 0) b = atomicAdd(&qc[Q_FETCH], kFetchChunk);
+      b = __shfl_sync(FULL, b, 0);
+      if (b >= total) exhausted = true;
+      else { w_next = b; w_end = min(b + kFetchChunk, total); }
+    }
+    int env = -1, meta = 0;
+    if (idx >= 0) {
+      const int2 q = queue[idx < n_long ? idx : N - 1 - (idx - n_long)];
+      env = q.x;
+      meta = q.y;
+    }
+    staged = __ballot_sync(FULL, idx >= 0);
+    unsigned taken = staged;
+    while (taken) {
+      const int src = __ffs(taken) - 1;
+      taken &= taken - 1;
+      const int e_src = __shfl_sync(FULL, env, src), m_src = __shfl_sync(FULL, meta, src);
+      const char* r_src = reinterpret_cast<const char*>(recs + (size_t)e_src * rec_words) + 16 * lane;
+      char* c_dst = reinterpret_cast<char*>(smem + (size_t)(warp_base + src) * col_stride) + 16 * lane;
+#pragma unroll
+      for (int k = 0; k < kMaxPieces; ++k) {
+        if (lane + 32 * k < rec16) {
+          const bool live = pc_off[k] < (int)((m_src >> pc_shift[k]) & 0xff) * pc_per[k];
+          cp_async16(c_dst + 512 * k, r_src + 512 * k, live ? 16 : 0);
+        }
+      }
+    }
+    return env;
+  }
+};
+
+
 template <typename T, bool FRICTION>
 __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
                                                   const int2* __restrict__ queue, int* __restrict__ qc, int col_stride,
@@ -489,30 +584,8 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
   T* const col = smem + (size_t)threadIdx.x * col_stride;
   const SolveLayout L = solve_layout(P);
   const int N = P.num_envs;
-  const int n_long = qc[Q_LONG], total = n_long + qc[Q_SHORT];
-  const unsigned lt = (1u << lane) - 1;
-  const int rec16 = (rec_words * (int)sizeof(T)) >> 4, hdr16 = (REC_ROWS * (int)sizeof(T)) >> 4;
-  // The record -> column copy: this lane moves the 16-byte pieces lane, lane + 32, ... of every
-  // record its warp takes.  What block a piece lies in never changes, so it is worked out once:
-  // piece k is live iff  pc_off[k] < count(pair pc_shift[k] / 8) * pc_per[k]   (header: always).
-  int pc_shift[kMaxPieces], pc_off[kMaxPieces], pc_per[kMaxPieces];
-#pragma unroll
-  for (int k = 0; k < kMaxPieces; ++k) {
-    const int i = lane + 32 * k;
-    pc_shift[k] = 0; pc_off[k] = (i < hdr16) ? -1 : 0x7fffffff; pc_per[k] = 0;  // header piece / outside every block
-#pragma unroll
-    for (int m = 0; m < 3; ++m) {
-      const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
-      const int lo = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4, per = (w * (int)sizeof(T)) >> 4;
-      if (i >= lo && i < lo + 4 * per) { pc_shift[k] = 8 * m; pc_off[k] = i - lo; pc_per[k] = per; }
-      if (L.fbase[m] >= 0) {
-        const int flo = ((REC_ROWS + L.fbase[m]) * (int)sizeof(T)) >> 4, fper = ((L.rpc[m] - 1) * w * (int)sizeof(T)) >> 4;
-        if (i >= flo && i < flo + 4 * fper) { pc_shift[k] = 8 * m; pc_off[k] = i - flo; pc_per[k] = fper; }
-      }
-    }
-  }
-  int w_next = 0, w_end = 0;  // the warp's slice of the queue (uniform)
-  bool exhausted = total == 0;
+  PoolFeed<T> feed;  // the warp's slice of the queue and the record -> column copy (shared with k_solve_lam)
+  feed.init(L, lane, rec_words, qc, N);
   SolveRegs<T> R;
   SolveScale<T> S;
   solve_consts(P, R, S);
@@ -537,47 +610,9 @@ __global__ void __launch_bounds__(kBlock) k_solve(const __grid_constant__ Params
       for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
     }
     const unsigned idle = ~busy_m;
-    if (idle && !exhausted && (idle == FULL || __popc(idle) >= fetch_min)) {
-      unsigned need = idle;
-      int idx = -1;
-      while (need && !exhausted) {
-        const int avail = w_end - w_next;
-        const int rank = __popc(need & lt);
-        const bool mine = ((need >> lane) & 1u) && rank < avail;
-        if (mine) idx = w_next + rank;
-        const unsigned got = __ballot_sync(FULL, mine);
-        need &= ~got;
-        w_next += __popc(got);
-        if (!need) break;
-        int b = 0;
-        if (lane == 0) b = atomicAdd(&qc[Q_FETCH], kFetchChunk);
-        b = __shfl_sync(FULL, b, 0);
-        if (b >= total) exhausted = true;
-        else { w_next = b; w_end = min(b + kFetchChunk, total); }
-      }
-      int env = -1, meta = 0;
-      if (idx >= 0) {
-        const int2 q = queue[idx < n_long ? idx : N - 1 - (idx - n_long)];
-        env = q.x;
-        meta = q.y;
-        rec = recs + (size_t)env * rec_words;
-      }
-      staged_m = __ballot_sync(FULL, idx >= 0);
-      unsigned taken = staged_m;
-      while (taken) {
-        const int src = __ffs(taken) - 1;
-        taken &= taken - 1;
-        const int e_src = __shfl_sync(FULL, env, src), m_src = __shfl_sync(FULL, meta, src);
-        const char* r_src = reinterpret_cast<const char*>(recs + (size_t)e_src * rec_words) + 16 * lane;
-        char* c_dst = reinterpret_cast<char*>(smem + (size_t)(warp_base + src) * col_stride) + 16 * lane;
-#pragma unroll
-        for (int k = 0; k < kMaxPieces; ++k) {
-          if (lane + 32 * k < rec16) {
-            const bool live = pc_off[k] < (int)((m_src >> pc_shift[k]) & 0xff) * pc_per[k];
-            cp_async16(c_dst + 512 * k, r_src + 512 * k, live ? 16 : 0);
-          }
-        }
-      }
+    if (idle && !feed.exhausted && (idle == FULL || __popc(idle) >= fetch_min)) {
+      const int env = feed.take(idle, lane, queue, qc, recs, rec_words, smem, warp_base, col_stride, staged_m);
+      if (env >= 0) rec = recs + (size_t)env * rec_words;
     }
     if (!busy_m) {
       if (!staged_m) break;
@@ -614,30 +649,9 @@ __global__ void __launch_bounds__(kBlock, 2) k_solve_lam(const __grid_constant__
   T* const col = smem + (size_t)threadIdx.x * col_stride;
   const SolveLayout L = solve_layout(P);
   const int N = P.num_envs;
-  const int n_long = qc[Q_LONG], total = n_long + qc[Q_SHORT];
   const unsigned lt = (1u << lane) - 1;
-  const int rec16 = (rec_words * (int)sizeof(T)) >> 4, hdr16 = (REC_ROWS * (int)sizeof(T)) >> 4;
-  // The record -> column copy: this lane moves the 16-byte pieces lane, lane + 32, ... of every
-  // record its warp takes.  What block a piece lies in never changes, so it is worked out once:
-  // piece k is live iff  pc_off[k] < count(pair pc_shift[k] / 8) * pc_per[k]   (header: always).
-  int pc_shift[kMaxPieces], pc_off[kMaxPieces], pc_per[kMaxPieces];
-#pragma unroll
-  for (int k = 0; k < kMaxPieces; ++k) {
-    const int i = lane + 32 * k;
-    pc_shift[k] = 0; pc_off[k] = (i < hdr16) ? -1 : 0x7fffffff; pc_per[k] = 0;  // header piece / outside every block
-#pragma unroll
-    for (int m = 0; m < 3; ++m) {
-      const int w = (m == BCP_PAIR_CART_POLE) ? (int)SW2 : (int)SW1;
-      const int lo = ((REC_ROWS + L.base[m]) * (int)sizeof(T)) >> 4, per = (w * (int)sizeof(T)) >> 4;
-      if (i >= lo && i < lo + 4 * per) { pc_shift[k] = 8 * m; pc_off[k] = i - lo; pc_per[k] = per; }
-      if (L.fbase[m] >= 0) {
-        const int flo = ((REC_ROWS + L.fbase[m]) * (int)sizeof(T)) >> 4, fper = ((L.rpc[m] - 1) * w * (int)sizeof(T)) >> 4;
-        if (i >= flo && i < flo + 4 * fper) { pc_shift[k] = 8 * m; pc_off[k] = i - flo; pc_per[k] = fper; }
-      }
-    }
-  }
-  int w_next = 0, w_end = 0;  // the warp's slice of the queue (uniform)
-  bool exhausted = total == 0;
+  PoolFeed<T> feed;  // the warp's slice of the queue and the record -> column copy (shared with k_solve)
+  feed.init(L, lane, rec_words, qc, N);
   SolveScale<T> S;
   {
     SolveRegs<T> R0;
@@ -671,47 +685,9 @@ __global__ void __launch_bounds__(kBlock, 2) k_solve_lam(const __grid_constant__
       for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, busy ? cnt[m] : 0);
     }
     const unsigned idle = ~busy_m;
-    if (idle && !exhausted && (idle == FULL || __popc(idle) >= fetch_min)) {
-      unsigned need = idle;
-      int idx = -1;
-      while (need && !exhausted) {
-        const int avail = w_end - w_next;
-        const int rank = __popc(need & lt);
-        const bool mine = ((need >> lane) & 1u) && rank < avail;
-        if (mine) idx = w_next + rank;
-        const unsigned got = __ballot_sync(FULL, mine);
-        need &= ~got;
-        w_next += __popc(got);
-        if (!need) break;
-        int b = 0;
-        if (lane == 0) b = atomicAdd(&qc[Q_FETCH], kFetchChunk);
-        b = __shfl_sync(FULL, b, 0);
-        if (b >= total) exhausted = true;
-        else { w_next = b; w_end = min(b + kFetchChunk, total); }
-      }
-      int env = -1, meta = 0;
-      if (idx >= 0) {
-        const int2 q = queue[idx < n_long ? idx : N - 1 - (idx - n_long)];
-        env = q.x;
-        meta = q.y;
-        rec = recs + (size_t)env * rec_words;
-      }
-      staged_m = __ballot_sync(FULL, idx >= 0);
-      unsigned taken = staged_m;
-      while (taken) {
-        const int src = __ffs(taken) - 1;
-        taken &= taken - 1;
-        const int e_src = __shfl_sync(FULL, env, src), m_src = __shfl_sync(FULL, meta, src);
-        const char* r_src = reinterpret_cast<const char*>(recs + (size_t)e_src * rec_words) + 16 * lane;
-        char* c_dst = reinterpret_cast<char*>(smem + (size_t)(warp_base + src) * col_stride) + 16 * lane;
-#pragma unroll
-        for (int k = 0; k < kMaxPieces; ++k) {
-          if (lane + 32 * k < rec16) {
-            const bool live = pc_off[k] < (int)((m_src >> pc_shift[k]) & 0xff) * pc_per[k];
-            cp_async16(c_dst + 512 * k, r_src + 512 * k, live ? 16 : 0);
-          }
-        }
-      }
+    if (idle && !feed.exhausted && (idle == FULL || __popc(idle) >= fetch_min)) {
+      const int env = feed.take(idle, lane, queue, qc, recs, rec_words, smem, warp_base, col_stride, staged_m);
+      if (env >= 0) rec = recs + (size_t)env * rec_words;
     }
     if (!busy_m) {
       if (!staged_m) break;
