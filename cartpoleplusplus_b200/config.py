@@ -16,7 +16,7 @@ from typing import Optional
 
 from . import urdf as _urdf
 
-BCP_ABI_VERSION = 7
+BCP_ABI_VERSION = 8
 DTYPE_F32, DTYPE_F64 = 0, 1
 REASON_NAMES = {0: None, 1: "out of position bounds", 2: "out of orientation bounds", 3: "episode length",
                 4: "resetting", 5: "fresh"}
@@ -98,6 +98,7 @@ class BcpConfig(ctypes.Structure):
         ("warmstart_factor", ctypes.c_double),
         ("gyro_term", ctypes.c_int32),
         ("reserved1", ctypes.c_int32),
+        ("cart_ground_friction", ctypes.c_double),
     ]
 
 
@@ -170,7 +171,7 @@ def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dt
     if g("gui", False):
         raise NotImplementedError("--gui needs a display: unavailable on this box")
     physics = physics or PhysicsParams()
-    ground, cart, pole = scene if scene is not None else _urdf.load_scene(g("model_dir", None))
+    ground, cart, pole = scene if scene is not None else _urdf.load_scene(g("model_dir", None), g("cart_model", "cart"))
     if g("cart_friction", None) is not None:
         cart = dataclasses.replace(cart, lateral_friction=float(opts.cart_friction))
 
@@ -207,6 +208,7 @@ def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dt
     c.angle_threshold = ANGLE_THRESHOLD
     c.sin_angle_threshold = math.sin(ANGLE_THRESHOLD)
     c.tan_angle_threshold = math.tan(ANGLE_THRESHOLD)
+    c.cart_ground_friction = -1.0 if cart.ground_friction is None else float(cart.ground_friction)
     _fill_body(c.ground, ground, INIT_POS["ground"], physics.inertia_from_file)
     off = (float(init_offset[0]), float(init_offset[1]), 0.0)
     _fill_body(c.cart, cart, tuple(a + b for a, b in zip(INIT_POS["cart"], off)), physics.inertia_from_file)

@@ -89,7 +89,9 @@ template <typename T> inline Params<T> make_params(const bcp_config& c) {
   for (int m = 0; m < 3; ++m) {
     const double ta = shape_breaking(c, *A[m]), tb = shape_breaking(c, *B[m]);
     p.breaking[m] = (T)(ta < tb ? ta : tb);
-    double f = A[m]->friction * B[m]->friction;
+    // the cart's friction against the ground may differ from its friction against the pole (compound cart, bcp.h)
+    const double fb = (m == BCP_PAIR_GROUND_CART && c.cart_ground_friction >= 0.0) ? c.cart_ground_friction : B[m]->friction;
+    double f = A[m]->friction * fb;
     if (f < -c.max_friction) f = -c.max_friction;
     if (f > c.max_friction) f = c.max_friction;
     p.mu[m] = (T)f;

@@ -53,6 +53,9 @@ def add_opts(parser: argparse.ArgumentParser) -> None:
     parser.add_argument("--no-carry-over-reset", action="store_true",
                         help="clear the pending force and contact caches on reset (deviation from pybullet)")
     parser.add_argument("--model-dir", type=str, default=None, help="directory with ground/cart/pole .urdf")
+    parser.add_argument("--cart-model", type=str, default="cart", choices=["cart", "double_cart"],
+                        help="cart: models/cart.urdf (bullet_cartpole.py:155); double_cart: the fork's compound cart of "
+                             "random_action_agent.py:781-794 - upper half friction 1.0 under the pole, lower half 0.0 on the ground")
 
 
 def default_opts(**overrides) -> argparse.Namespace:

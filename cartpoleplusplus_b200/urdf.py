@@ -41,6 +41,10 @@ class BoxBody:
     contact_cfm: Optional[float] = None
     contact_erp: Optional[float] = None
     rgba: Tuple[float, float, float, float] = (1.0, 1.0, 1.0, 1.0)  # <visual><material><color rgba>: the pixel observation's colours
+    # compound bodies (parse_compound_cart_urdf): the friction of the half that touches the ground, and the composite
+    # inertia diagonal with <inertia_scaling> already applied link by link
+    ground_friction: Optional[float] = None
+    composite_inertia: Optional[Tuple[float, float, float]] = None
 
     @property
     def half_extents(self) -> Tuple[float, float, float]:
@@ -55,6 +59,8 @@ class BoxBody:
     def effective_inertia(self, inertia_from_file: bool = False) -> Tuple[float, float, float]:
         if self.mass == 0.0:
             return (0.0, 0.0, 0.0)
+        if self.composite_inertia is not None:
+            return self.composite_inertia
         base = self.inertia_file if inertia_from_file else self.box_inertia()
         return tuple(self.inertia_scaling * v for v in base)
 
@@ -116,7 +122,80 @@ def parse_box_urdf(path: str) -> BoxBody:
     )
 
 
-def load_scene(model_dir: Optional[str] = None):
+def parse_compound_cart_urdf(path: str, inertia_from_file: bool = False) -> BoxBody:
+    """The fork's two-link cart (reference models/double_cart_1.urdf:15-80): two box links glued by a fixed joint, the
+    upper one with friction against the pole, the lower one frictionless against the ground.
+
+    pybullet builds a btMultiBody whose base is the parent link and whose one link hangs on a fixed (0-DOF) joint: it
+    moves as ONE rigid body - the composite of the two halves - with two colliders that keep their own friction
+    ([BULLET-RECALL]).  This parser returns that composite as a single box body:
+      * mass = sum; inertia about the composite centre = sum over the links of (link inertia x its <inertia_scaling>,
+        about the link's own centre: box formula unless inertia_from_file) + the parallel-axis term m d^2, which the
+        scaling does not touch;
+      * collision box = the union of the two flush halves (checked: same footprint, stacked without gap or overlap);
+      * lateral_friction = the UPPER half's (what the pole touches), ground_friction = the LOWER half's (what the ground
+        touches).
+    Exactness of the single-box reduction: the pole touches the upper half's top face and the ground the lower half's
+    bottom face - where the two-collider world and this body produce the same contact points with the same friction.  A
+    pole leaning against the cart's side, or a cart lying on its side, would touch BOTH halves in the two-collider world;
+    here every cart-pole contact then takes the upper friction and every ground-cart contact the lower one (stated in
+    DESIGN.md section 11; the fork's game ends an episode long before)."""
+    root = ET.parse(path).getroot()
+    links = {l.attrib["name"]: l for l in root.findall("link")}
+    joints = root.findall("joint")
+    if len(links) != 2 or len(joints) != 1 or joints[0].attrib.get("type") != "fixed":
+        raise ValueError(f"{path}: expected two links glued by one fixed joint")
+    jo = joints[0].find("origin")
+    if jo is not None and (any(float(v) for v in jo.attrib.get("xyz", "0 0 0").split()) or any(float(v) for v in jo.attrib.get("rpy", "0 0 0").split())):
+        raise ValueError(f"{path}: joint origin offset not supported")
+    parts = []
+    for name in (joints[0].find("parent").attrib["link"], joints[0].find("child").attrib["link"]):
+        link = links[name]
+        inertial, collision, contact = link.find("inertial"), link.find("collision"), link.find("contact")
+        com = [float(v) for v in inertial.find("origin").attrib.get("xyz", "0 0 0").split()]
+        cxyz = [float(v) for v in collision.find("origin").attrib.get("xyz", "0 0 0").split()]
+        if com != cxyz or com[0] or com[1]:
+            raise ValueError(f"{path}: link {name}: collision box must be centred on the link's centre of mass, on the z axis")
+        size = tuple(float(v) for v in collision.find("geometry/box").attrib["size"].split())
+        ia = inertial.find("inertia").attrib
+        color = link.find("visual/material/color")
+        parts.append(dict(mass=float(inertial.find("mass").attrib["value"]), z=com[2], size=size,
+                          inertia_file=(float(ia["ixx"]), float(ia["iyy"]), float(ia["izz"])),
+                          friction=_value(contact, "lateral_friction", BULLET_DEFAULT_FRICTION),
+                          restitution=_value(contact, "restitution", BULLET_DEFAULT_RESTITUTION),
+                          scaling=_value(contact, "inertia_scaling", 1.0),
+                          rgba=tuple(float(v) for v in color.attrib["rgba"].split()) if color is not None else (1.0, 1.0, 1.0, 1.0)))
+    upper, lower = sorted(parts, key=lambda q: -q["z"])
+    if upper["size"][:2] != lower["size"][:2] or abs((upper["z"] - upper["size"][2] / 2) - (lower["z"] + lower["size"][2] / 2)) > 1e-12:
+        raise ValueError(f"{path}: the two boxes must share a footprint and be flush")
+    mass = upper["mass"] + lower["mass"]
+    zc = (upper["mass"] * upper["z"] + lower["mass"] * lower["z"]) / mass
+    top, bottom = upper["z"] + upper["size"][2] / 2, lower["z"] - lower["size"][2] / 2
+    if abs(zc - (top + bottom) / 2) > 1e-12:
+        raise ValueError(f"{path}: composite centre of mass off the box centre: not supported")
+    inertia = [0.0, 0.0, 0.0]
+    for q in (upper, lower):
+        lx, ly, lz = q["size"]
+        own = q["inertia_file"] if inertia_from_file else (q["mass"] / 12 * (ly * ly + lz * lz), q["mass"] / 12 * (lx * lx + lz * lz), q["mass"] / 12 * (lx * lx + ly * ly))
+        d2 = (q["z"] - zc) ** 2
+        for i, par in enumerate((d2, d2, 0.0)):
+            inertia[i] += q["scaling"] * own[i] + q["mass"] * par
+    return BoxBody(name=root.attrib.get("name", os.path.basename(path)), mass=mass, inertia_file=tuple(inertia),
+                   box_size=(upper["size"][0], upper["size"][1], top - bottom), lateral_friction=upper["friction"],
+                   restitution=upper["restitution"], inertia_scaling=1.0, rgba=upper["rgba"],
+                   ground_friction=lower["friction"], composite_inertia=tuple(inertia))
+
+
+def load_scene(model_dir: Optional[str] = None, cart_model: str = "cart"):
+    """(ground, cart, pole); cart_model 'double_cart' loads the fork's compound cart (models/double_cart.urdf)."""
+    if cart_model == "double_cart":
+        d = model_dir or MODEL_DIR
+        return (parse_box_urdf(os.path.join(d, "ground.urdf")), parse_compound_cart_urdf(os.path.join(d, "double_cart.urdf")),
+                parse_box_urdf(os.path.join(d, "pole.urdf")))
+    return _load_scene(model_dir)
+
+
+def _load_scene(model_dir: Optional[str] = None):
     """(ground, cart, pole) parsed from `model_dir` (default: the packaged models)."""
     d = model_dir or MODEL_DIR
     return tuple(parse_box_urdf(os.path.join(d, f"{n}.urdf")) for n in ("ground", "cart", "pole"))

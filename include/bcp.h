@@ -26,7 +26,7 @@
 extern "C" {
 #endif
 
-#define BCP_ABI_VERSION 7
+#define BCP_ABI_VERSION 8
 
 /* ---- dtype of the physics arithmetic ------------------------------------ */
 #define BCP_DTYPE_F32 0 /* fast mode                                          */
@@ -128,6 +128,9 @@ typedef struct bcp_config {
                                 README's stability known answer pins; 0 = off   */
   int32_t gyro_term;         /* 1 */
   int32_t reserved1;
+  double cart_ground_friction; /* >= 0: lateral friction of the cart AGAINST THE GROUND, when it differs from cart.friction
+                                  (what the pole touches): the fork's compound cart, models/double_cart_1.urdf:15-80 - upper half
+                                  1.0, lower half 0.0.  < 0: cart.friction serves both pairs (cart.urdf)                       */
 } bcp_config;
 
 /* ---- canonical per-env state record (doubles), used by get/set_state ------

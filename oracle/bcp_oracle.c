@@ -1085,6 +1085,11 @@ static void substep(const bcp_config* cfg, ostate* st, osubstep_info* info) {
     m = order[k];
     mf = &st->mani[m];
     mu = combine_friction(cfg, cb[pairA[m]], cb[pairB[m]]);
+    if (m == BCP_PAIR_GROUND_CART && cfg->cart_ground_friction >= 0.0) { /* compound cart: the lower half touches the ground */
+      bcp_body lower = cfg->cart;
+      lower.friction = cfg->cart_ground_friction;
+      mu = combine_friction(cfg, &cfg->ground, &lower);
+    }
     rest = (real)(cb[pairA[m]]->restitution * cb[pairB[m]]->restitution);
     for (j = 0; j < mf->count; ++j) {
       const int fi = n_n;

@@ -43,7 +43,26 @@ def add_opts_defaults():
     return flags
 
 
+def compound_constants(name):
+    """the two links of a double_cart URDF (models/double_cart_1.urdf:15-80) and its joint"""
+    root = ET.parse(os.path.join(REF, "models", name + ".urdf")).getroot()
+    out = {"links": {}, "joint": {"type": root.find("joint").attrib["type"], "parent": root.find("joint/parent").attrib["link"],
+                                   "child": root.find("joint/child").attrib["link"]}}
+    for link in root.findall("link"):
+        inertia = link.find("inertial/inertia").attrib
+        out["links"][link.attrib["name"]] = {
+            "mass": float(link.find("inertial/mass").attrib["value"]),
+            "com": [float(v) for v in link.find("inertial/origin").attrib["xyz"].split()],
+            "inertia": [float(inertia[k]) for k in ("ixx", "iyy", "izz")],
+            "box": [float(v) for v in link.find("collision/geometry/box").attrib["size"].split()],
+            "box_origin": [float(v) for v in link.find("collision/origin").attrib["xyz"].split()],
+            "contact": {c.tag: float(c.attrib["value"]) for c in link.find("contact")}}
+    return out
+
+
 if __name__ == "__main__":
+    json.dump({n: compound_constants(n) for n in ("double_cart_1", "double_cart_2")},
+              open(os.path.join(HERE, "double_cart_constants.json"), "w"), indent=1, sort_keys=True)
     json.dump({n: urdf_constants(n) for n in ("ground", "cart", "pole")},
               open(os.path.join(HERE, "model_constants.json"), "w"), indent=1, sort_keys=True)
     json.dump(add_opts_defaults(), open(os.path.join(HERE, "add_opts_defaults.json"), "w"), indent=1, sort_keys=True)

@@ -102,3 +102,33 @@ def test_step_after_done_and_errors(built):
     obs2, rew2, done2, info2 = env.step(torch.zeros(8, dtype=torch.int64).cuda())
     assert torch.equal(obs2, obs) and (rew2 == 0).all() and done2.all()
     env.close()
+
+
+def test_compound_cart_fp64_bit_exact_and_fp32_classified(built):
+    """the fork's compound cart (models/double_cart_1.urdf:15-80; --cart-model double_cart): fp64 kernel == oracle bit for
+    bit over a rollout with resets; one env.step of the fp32 split pipeline (row space: the cart-pole rows have friction)
+    within 1e-4 of the oracle or a classified decision flip."""
+    import torch
+    import parity_util as PU
+    n = 256
+    env, ora = _mk("fp64", n, False, initial_force=55.0, action_force=100.0, cart_model="double_cart", steps_per_repeat=2)
+    assert np.array_equal(env.reset().cpu().numpy(), ora.reset())
+    rng = np.random.default_rng(3)
+    for t in range(20):
+        a = rng.uniform(-1, 1, size=(n, 2)).astype(np.float32)
+        obs, rew, done, info = env.step(torch.from_numpy(a).cuda())
+        o = ora.step(a)
+        assert np.array_equal(obs.cpu().numpy(), o[0]) and np.array_equal(done.cpu().numpy(), o[2]), t
+    assert np.array_equal(env.get_state(), ora.state)
+    env.close()
+    n = 8192
+    env32, _ = _mk("fp32", n, False, initial_force=55.0, action_force=100.0, cart_model="double_cart", action_repeats=1, auto_reset="pipelined")
+    assert env32.solver_kind == "split/row-space"
+    from oracle import Oracle
+    ora64 = Oracle(env32.cfg, dtype="fp64")
+    state = PU.stationary_mix(env32, 600)
+    rep = PU.classify_step(env32, ora64, state, rng.uniform(-1, 1, size=(n, 2)).astype(np.float32), rng=rng)
+    rep.pop("dev"), rep.pop("spread")
+    print(rep)
+    assert rep["median"] <= 1e-6 and rep["q99"] <= 1e-4 and not rep["unexplained"] and not rep["bookkeeping_unexplained"], rep
+    env32.close()
