@@ -373,33 +373,38 @@ def run_ours(args):
     # copy of its observations, rewards and done flags are inside the timed region, and the host reads every reward).
     # The batch is driven the way a throughput-oriented host loop drives it - as two half batches, double buffered
     # (step_host_begin / step_host_end): while one half's outputs cross PCIe and are read, the other half steps ----
-    nh = [n // 2, n - n // 2]
-    halves = []
-    for i in range(2):
+    parts = max(1, args.e2e_parts)
+    nh = [n // parts] * (parts - 1) + [n - (n // parts) * (parts - 1)]
+    halves, off = [], 0
+    for i in range(parts):
         he = BatchedBulletCartpole(opts, discrete_actions=False, num_envs=nh[i], device=local, dtype=args.dtype, seed=args.seed,
-                                   env_id_offset=rank * n + (0 if i == 0 else nh[0]))
+                                   env_id_offset=rank * n + off)
+        off += nh[i]
         he.reset(copy=False)
         he.rollout_random(args.mix_calls)
         halves.append(he)
-    host_actions = [[torch.empty((nh[i], 2), dtype=torch.float32).pin_memory().uniform_(-1, 1) for _ in range(2)] for i in range(2)]
+    host_actions = [[torch.empty((nh[i], 2), dtype=torch.float32).pin_memory().uniform_(-1, 1) for _ in range(2)] for i in range(parts)]
     Ke = max(3, K)
     for t in range(2):
-        for i in range(2):
+        for i in range(parts):
             halves[i].step_host(host_actions[i][t % 2])
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
     e2e_live = 0
     t0 = time.perf_counter()
-    halves[0].step_host_begin(host_actions[0][0])
+    # every part is always either in flight or being read: begin(0..parts-2) up front, then per part: begin the one that was
+    # read longest ago, wait for the oldest in flight, read its rewards
+    for i in range(parts - 1):
+        halves[i].step_host_begin(host_actions[i][0])
     for t in range(Ke):
-        halves[1].step_host_begin(host_actions[1][t % 2])
-        _, rew, _, _ = halves[0].step_host_end()
-        e2e_live += int(rew.sum().item())
-        if t + 1 < Ke:
-            halves[0].step_host_begin(host_actions[0][(t + 1) % 2])
-        _, rew, _, _ = halves[1].step_host_end()
-        e2e_live += int(rew.sum().item())
+        for i in range(parts):
+            j = (i + parts - 1) % parts          # the part whose previous results were consumed longest ago
+            tj = t if j >= i else t + 1          # its step index
+            if tj < Ke:
+                halves[j].step_host_begin(host_actions[j][tj % 2])
+            _, rew, _, _ = halves[i].step_host_end()
+            e2e_live += int(rew.sum().item())
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     sampler.stop_flag = True
@@ -516,7 +521,7 @@ def run_ours(args):
         "kernel_ms_note": f"serialised (cohorts one after the other, {prof_calls} untimed profiled calls); the timed steps overlap the cohorts",
         "e2e": {"value": e2e_live_all / (e2e_ms * 1e-3), "unit": "env-steps/s",
                 "h2d_bytes_per_step": h2d_bytes, "d2h_bytes_per_step": d2h_bytes,
-                "how": "step_host_begin / step_host_end on two half batches, double buffered; every step's H2D and D2H inside the timed region"},
+                "how": f"step_host_begin / step_host_end on {parts} parts of the batch, multi-buffered; every step's H2D and D2H inside the timed region"},
         "gpu_launches": int(launches),
         "clocks": sampler.summary(),
         # BASELINE.json's metric is "% FP32 peak": the path is bound by the FP32 CUDA-core pipe (no contraction, arithmetic
@@ -628,6 +633,7 @@ def main():
     ap.add_argument("--span", type=int, default=200, help="env.steps the timed steps are spread over (>= --steps: every span/steps-th step is timed)")
     ap.add_argument("--no-configs3", action="store_true", help="N >= 2: skip the configs[3] run (1 M envs sharded, deciles)")
     ap.add_argument("--configs3-envs", type=int, default=1048576)
+    ap.add_argument("--e2e-parts", type=int, default=2, help="the e2e host loop drives the batch as this many parts, multi-buffered")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the upstream-style (friction, R*S = 10) workload reported beside the headline")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work of the cpu_baseline sample")
