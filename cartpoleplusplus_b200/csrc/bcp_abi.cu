@@ -188,11 +188,13 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
       const size_t rw = bcp::split_record_words(h->p32);
       A((void**)&h->recs, rw * N * sizeof(float));
       h->use_lam = bcp::split_uses_lambda(h->p32) ? 1 : 0;
-      // two cohorts from 32 768 envs up, then one per 65 536 envs, at most 8 (measured on B200: 65 536 envs as 2 x 32 768
-      // 0.355 -> 0.316 ms per env.step; 131 072 as 2 x 65 536 0.584 -> 0.519; 262 144 as 4, 1 M as 8); BCP_COHORTS overrides
+      // two cohorts from 32 768 envs, four from 65 536, then one per 131 072, at most 8 (measured on B200 with the call as a CUDA
+      // graph: 65 536 envs as 1 / 2 / 3 / 4 cohorts 0.355 / 0.311 / 0.307 / 0.302 ms per env.step; 131 072 as 2 or 4: 0.52;
+      // 262 144 as 4: 1.00, as 8: 1.00; 1 M as 8: 3.9); BCP_COHORTS overrides
       const char* cv = getenv("BCP_COHORTS");
-      int nc = cv ? atoi(cv) : (cfg->num_envs >= 32768 ? (cfg->num_envs + 65535) / 65536 : 1);
-      if (!cv && cfg->num_envs >= 32768 && nc < 2) nc = 2;
+      int nc = 1;
+      if (cv) nc = atoi(cv);
+      else if (cfg->num_envs >= 32768) nc = cfg->num_envs < 65536 ? 2 : (cfg->num_envs <= 262144 ? 4 : (cfg->num_envs + 131071) / 131072);
       if (nc < 1) nc = 1;
       if (nc > 8) nc = 8;
       while (nc > 1 && cfg->num_envs / nc < 1024) nc--;
