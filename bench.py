@@ -228,7 +228,10 @@ def pin_near_gpu(local, world):
         k, m = same.index(local) if local in same else 0, max(1, len(same))
         share = allowed[k * len(allowed) // m:(k + 1) * len(allowed) // m] or allowed
         os.sched_setaffinity(0, share)
-        torch.set_num_threads(max(1, min(4, len(share))))
+        # the host side of a step is a 65 536-float sum and a byte scan: one thread does it; more threads only spin on
+        # the few cores a rank has when several ranks share the host (N = 8 on 32 cores: 4 each)
+        # (measured: N = 2, e2e / value 0.57 with 4 torch threads per rank, 0.72 with 1; N = 1 with 16 cores to itself: 0.78 vs 0.74)
+        torch.set_num_threads(int(os.environ.get("BCP_BENCH_TORCH_THREADS", "1" if world > 1 else str(max(1, min(4, len(share)))))))
         return {"numa_node": node, "pinned": True, "cpus": len(share), "torch_threads": torch.get_num_threads()}
     except Exception as e:  # no sysfs / no permission: run unpinned and say so
         return {"pinned": False, "why": str(e)[:80]}
