@@ -288,9 +288,11 @@ int bcp_reset(bcp_env* h, const uint8_t* mask, float* obs_out, void* stream) {
 }  // extern "C"
 
 // one call of every cohort, enqueued on `s` and the cohorts' own streams (forked from and joined back into `s`)
+// slabs: `obs_out` is repeat-major, [R][num_envs][2][7] (bcp_step_host), instead of the (num_envs, R, 2, 7) block
 static int enqueue_split(bcp_env* h, const void* actions, float* obs_out, float* reward_out, uint8_t* done_out, uint8_t* reason_out,
-                         cudaStream_t s, int* launches) {
-  const int width = 14 * h->cfg.action_repeats;
+                         cudaStream_t s, int* launches, bool slabs = false) {
+  const size_t env_stride = slabs ? 14 : (size_t)14 * h->cfg.action_repeats;
+  const size_t rep_stride = slabs ? (size_t)14 * h->cfg.num_envs : 14;
   const size_t abytes = h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float);
   // while the kernels are being bracketed by events (bcp_profile_begin) the cohorts run one after the other on the
   // caller's stream, so that a kernel's time is its own
@@ -306,10 +308,10 @@ static int enqueue_split(bcp_env* h, const void* actions, float* obs_out, float*
     co.b.after_prep = h->split_hook;
     co.b.hook_ctx = h->split_hook ? &h->hook_args[c] : nullptr;
     CK(bcp::launch_step_split(co.P, (float*)h->fdata + b * bcp::NF, h->idata + b * bcp::NI, co.b,
-                              static_cast<const char*>(actions) + b * abytes, obs_out ? obs_out + b * width : nullptr,
+                              static_cast<const char*>(actions) + b * abytes, obs_out ? obs_out + b * env_stride : nullptr,
                               reward_out ? reward_out + b : nullptr, done_out ? done_out + b : nullptr,
                               reason_out ? reason_out + b : nullptr, h->stats(), cs, launches,
-                              h->profiling ? &h->prof_events : nullptr));
+                              h->profiling ? &h->prof_events : nullptr, env_stride, rep_stride));
     if (h->profiling) h->prof_calls.push_back((int)(h->prof_events.size() - ev0));
     if (fork && c > 0) {
       CK(cudaEventRecord(co.ev_done, cs));
@@ -331,7 +333,11 @@ int bcp_step(bcp_env* h, const void* actions, float* obs_out, float* reward_out,
     // Steady state: the whole call - every cohort's memsets and kernels, the forks to the cohort and side streams and their
     // joins - is one CUDA graph launch (the host then spends ~10 us per env.step instead of one launch call per kernel).
     // Captured the first time a (outputs, stream, visiting-order parity) combination is seen after the handle's first call.
-    const bool plain = h->use_graph && !h->profiling && !h->trace && !h->split_hook && h->cohorts[0].b.cur >= 0 && h->cohorts[0].b.side_ready;
+    // (a caller that is itself capturing `stream` gets the plain stream launches, which its capture records)
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    if (cudaStreamIsCapturing(s, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+    const bool plain = h->use_graph && cap == cudaStreamCaptureStatusNone && !h->profiling && !h->trace && !h->split_hook &&
+                       h->cohorts[0].b.cur >= 0 && h->cohorts[0].b.side_ready;
     if (plain) {
       const size_t abytes = (size_t)h->cfg.num_envs * (h->cfg.discrete_actions ? sizeof(int32_t) : 2 * sizeof(float));
       const int parity = h->cohorts[0].b.cur;
@@ -424,7 +430,10 @@ void host_step_hook(void* ctx, int k, cudaStream_t s) {
   cudaEventRecord(co.ev_prep[k], s);
   if (!last) return;
   for (bcp_env::Cohort& c : h->cohorts) cudaStreamWaitEvent(h->hs.copy, c.ev_prep[k], 0);
-  pack_and_copy(h, k / S - 1, h->hs.copy);
+  {  // the kernels wrote repeat r straight into its slab: no pack kernel, just the copy
+    const size_t n = (size_t)h->cfg.num_envs, r = (size_t)(k / S - 1);
+    cudaMemcpyAsync(h->hs.h_obs + r * n * 14, h->hs.d_slab + r * n * 14, n * 14 * sizeof(float), cudaMemcpyDeviceToHost, h->hs.copy);
+  }
   cudaEventRecord(h->hs.ev_copied, h->hs.copy);
   h->hs.fired = true;
 }
@@ -455,19 +464,46 @@ static int host_step_enqueue(bcp_env* h, const void* h_actions, float* h_obs_rm,
   h->hs.h_obs = h_obs_rm;
   h->hs.fired = false;
   if (split) {
+    // Split pipeline: k_prep writes the observation of repeat r straight into slab r of the device block
+    // [R slabs | reward | done | reason]; slab r leaves as soon as every cohort's k_prep that completes it is done, and the last
+    // slab leaves together with reward, done and reason - ONE copy when the caller's buffers are laid out the same way.
+    float* s_obs = h->hs.d_slab;
+    float* s_rew = h->hs.d_slab + n * R * 14;
+    uint8_t* s_done = reinterpret_cast<uint8_t*>(s_rew + n);
+    uint8_t* s_reason = s_done + n;
     h->hook_args.resize(h->cohorts.size());
     for (size_t c = 0; c < h->cohorts.size(); ++c) h->hook_args[c] = bcp_env::HookArg{h, (int)c};
     h->split_hook = host_step_hook;
+    int nl = 0;
+    const int rc = enqueue_split(h, h->hs.d_act, s_obs, s_rew, s_done, s_reason, s, &nl, true);
+    h->split_hook = nullptr;
+    h->launches += nl;
+    if (h->hs.h2d_pending) {  // the call failed before its first kernel
+      cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);
+      h->hs.h2d_pending = false;
+    }
+    if (rc) return rc;
+    const size_t r0 = h->hs.fired ? R - 1 : 0;  // repeats that did not leave during the call
+    float* h_from = h_obs_rm + r0 * n * 14;
+    const float* d_from = s_obs + r0 * n * 14;
+    const size_t obs_bytes = (R - r0) * n * 14 * sizeof(float);
+    if (reinterpret_cast<uint8_t*>(h_obs_rm) + ob == reinterpret_cast<uint8_t*>(h_reward) && reinterpret_cast<uint8_t*>(h_reward) + rb == h_done &&
+        h_done + n == h_reason) {
+      CK(cudaMemcpyAsync(h_from, d_from, obs_bytes + rb + 2 * n, cudaMemcpyDeviceToHost, s));
+    } else {
+      CK(cudaMemcpyAsync(h_from, d_from, obs_bytes, cudaMemcpyDeviceToHost, s));
+      CK(cudaMemcpyAsync(h_reward, s_rew, rb, cudaMemcpyDeviceToHost, s));
+      CK(cudaMemcpyAsync(h_done, s_done, n, cudaMemcpyDeviceToHost, s));
+      CK(cudaMemcpyAsync(h_reason, s_reason, n, cudaMemcpyDeviceToHost, s));
+    }
+    if (h->hs.fired) CK(cudaStreamWaitEvent(s, h->hs.ev_copied, 0));  // a sync on `stream` covers the early slabs too
+    CK(cudaGetLastError());
+    return 0;
   }
+  // one-launch pipelines (fp64, small batches): bcp_step into the (B, R, 2, 7) block, then pack and copy every repeat
   const int rc = bcp_step(h, h->hs.d_act, d_obs, d_rew, d_done, d_reason, (void*)s);
-  h->split_hook = nullptr;
-  if (h->hs.h2d_pending) {  // the call failed before its first kernel
-    cudaStreamWaitEvent(s, h->hs.ev_h2d, 0);
-    h->hs.h2d_pending = false;
-  }
   if (rc) return rc;
-  // the repeats that did not leave during the call (all of them on the one-launch pipeline)
-  for (int r = h->hs.fired ? (int)R - 1 : 0; r < (int)R; ++r) pack_and_copy(h, r, s);
+  for (int r = 0; r < (int)R; ++r) pack_and_copy(h, r, s);
   if (reinterpret_cast<uint8_t*>(h_reward) + rb == h_done && h_done + n == h_reason) {
     CK(cudaMemcpyAsync(h_reward, d_rew, rb + 2 * n, cudaMemcpyDeviceToHost, s));  // one transfer when the caller's buffers are adjacent
   } else {
@@ -475,7 +511,6 @@ static int host_step_enqueue(bcp_env* h, const void* h_actions, float* h_obs_rm,
     CK(cudaMemcpyAsync(h_done, d_done, n, cudaMemcpyDeviceToHost, s));
     CK(cudaMemcpyAsync(h_reason, d_reason, n, cudaMemcpyDeviceToHost, s));
   }
-  if (h->hs.fired) CK(cudaStreamWaitEvent(s, h->hs.ev_copied, 0));  // a sync on `stream` covers the early slabs too
   CK(cudaGetLastError());
   return 0;
 }
@@ -494,10 +529,10 @@ int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_r
   if (!h->hs.d_out) {
     CK(cudaMalloc(&h->hs.d_act, ab));
     CK(cudaMalloc((void**)&h->hs.d_out, ob + rb + 2 * n));
-    CK(cudaMalloc((void**)&h->hs.d_slab, ob));
+    CK(cudaMalloc((void**)&h->hs.d_slab, ob + rb + 2 * n));  // [R slabs | reward | done | reason]
     // an env that is mid-reset keeps its previous observation in the output block (bcp_step writes nothing there): start from zeros like the caller's own buffers
     CK(cudaMemsetAsync(h->hs.d_out, 0, ob + rb + 2 * n, s));
-    CK(cudaMemsetAsync(h->hs.d_slab, 0, ob, s));
+    CK(cudaMemsetAsync(h->hs.d_slab, 0, ob + rb + 2 * n, s));
     {
       int lo = 0, hi = 0;
       cudaDeviceGetStreamPriorityRange(&lo, &hi);
@@ -509,8 +544,10 @@ int bcp_step_host(bcp_env* h, const void* h_actions, float* h_obs_rm, float* h_r
   }
   // Steady state on the split pipeline: the whole host call - H2D of the actions, every cohort's kernels, the slab packs
   // and the D2H copies into the caller's (pinned, pointer-stable) buffers - is one CUDA graph per (buffers, parity).
-  const bool can_graph = h->use_graph && !h->f64() && h->use_split && !h->profiling && !h->trace && h->cohorts[0].b.cur >= 0 &&
-                         h->cohorts[0].b.side_ready;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(s, &cap) != cudaSuccess) { cudaGetLastError(); cap = cudaStreamCaptureStatusNone; }
+  const bool can_graph = h->use_graph && cap == cudaStreamCaptureStatusNone && !h->f64() && h->use_split && !h->profiling && !h->trace &&
+                         h->cohorts[0].b.cur >= 0 && h->cohorts[0].b.side_ready;
   if (can_graph) {
     const int parity = h->cohorts[0].b.cur;
     bcp_env::HostGraph* hg = nullptr;

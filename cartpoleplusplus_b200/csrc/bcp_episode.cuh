@@ -117,7 +117,9 @@ template <typename T> BCP_HD void post_substep(const Params<T>& P, Env<T>& st, i
   }
 }
 // steps / done / reward bookkeeping (:239-260); returns the reason code, `live` = reward 1
-template <typename T> BCP_HD int call_end(const Params<T>& P, Env<T>& st, int mode, float* obs, bool& live) {
+// rep_stride: floats between two repeats of one env in `obs` (14 in the (B, R, 2, 7) block; 14 * B in the repeat-major slabs
+// bcp_step_host sends to the host)
+template <typename T> BCP_HD int call_end(const Params<T>& P, Env<T>& st, int mode, float* obs, bool& live, size_t rep_stride = 14) {
   live = mode == MODE_LIVE;
   if (mode == MODE_LIVE) {
     st.steps += 1;  // :239
@@ -126,7 +128,7 @@ template <typename T> BCP_HD int call_end(const Params<T>& P, Env<T>& st, int mo
     return reason;
   }
   if (mode == MODE_FRESH) {
-    if (obs) for (int r = 0; r < P.R; ++r) write_obs(st, obs + 14 * r);
+    if (obs) for (int r = 0; r < P.R; ++r) write_obs(st, obs + rep_stride * r);
     return BCP_REASON_FRESH;
   }
   return mode == MODE_RESET ? BCP_REASON_RESETTING : BCP_REASON_NONE;

@@ -159,9 +159,9 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
 }
 cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers& b, const void* actions, float* obs,
                               float* reward, uint8_t* done, uint8_t* reason, StatsPtrs sp, cudaStream_t s, int* launches,
-                              std::vector<cudaEvent_t>* prof) {
+                              std::vector<cudaEvent_t>* prof, size_t obs_env_stride, size_t obs_rep_stride) {
   const Stats st{sp.hist, sp.header, sp.reward_sum};
-  const SplitIO io{actions, obs, reward, done, reason};
+  const SplitIO io{actions, obs, reward, done, reason, obs_env_stride ? obs_env_stride : (size_t)14 * P.R, obs_rep_stride ? obs_rep_stride : (size_t)14};
   if (P.any_friction) return step_split_impl<true>(P, f, id, b, io, st, s, launches, prof);
   return step_split_impl<false>(P, f, id, b, io, st, s, launches, prof);
 }

@@ -60,9 +60,10 @@ size_t split_record_words(const Params<float>& P);
 size_t split_counter_words(const Params<float>& P);
 // `prof` (optional): an event is appended before the first kernel and after every kernel, so
 // consecutive events bracket k_prep, k_solve, k_prep, ... of the call.
+// obs_env_stride / obs_rep_stride (floats; 0 = the (B, R, 2, 7) block: 14 R and 14): where env e, repeat r goes in `obs`.
 cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBuffers& b, const void* actions, float* obs,
                               float* reward, uint8_t* done, uint8_t* reason, StatsPtrs stats, cudaStream_t s,
-                              int* launches, std::vector<cudaEvent_t>* prof);
+                              int* launches, std::vector<cudaEvent_t>* prof, size_t obs_env_stride = 0, size_t obs_rep_stride = 0);
 
 cudaError_t launch_fma_peak(int use_f64, int iters, double* tflops);
 cudaError_t launch_compact(const uint8_t* flag, int n, int* list, int* count, cudaStream_t s);

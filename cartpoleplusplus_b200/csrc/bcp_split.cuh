@@ -261,6 +261,9 @@ struct SplitIO {
   float* reward;
   uint8_t* done;
   uint8_t* reason;
+  // layout of `obs`: floats between two envs and between two repeats of an env.  (14 R, 14): the (B, R, 2, 7) block of
+  // bcp_step; (14, 14 B): repeat-major slabs [R][B][2][7], what bcp_step_host copies to the host slab by slab
+  size_t env_stride, rep_stride;
 };
 
 // Visiting order of the envs.  The kernel that closes a call files every env under its contact
@@ -324,7 +327,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   const int64_t genv = P.env_id_offset + e;
   const int width = 14 * P.R;
   T* rec = recs + (size_t)(valid ? e : 0) * rec_words;
-  float* obs = (io.obs && valid) ? io.obs + (size_t)e * width : nullptr;
+  float* obs = (io.obs && valid) ? io.obs + (size_t)e * io.env_stride : nullptr;
   Env<T> st;
   st.done = 1;
   st.reset_left = 0;
@@ -373,7 +376,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     T fx, fy;
     action_force(P, a, ax, ay, fx, fy);
     post_substep(P, st, genv, mode, fx, fy);
-    if ((s_fin + 1) % P.S == 0 && mode == MODE_LIVE && obs) write_obs(st, obs + 14 * (s_fin / P.S));  // :237
+    if ((s_fin + 1) % P.S == 0 && mode == MODE_LIVE && obs) write_obs(st, obs + io.rep_stride * (s_fin / P.S));  // :237
   }
   if (s_set >= 0) {
     const bool on = valid && substep_on(mode, st);
@@ -436,7 +439,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   } else {  // the call closes: steps / done / reward (:239-260), outputs, episode statistics
     if (fin) for (int m = 0; m < 3; ++m) finish_impulses(f, e, m, st.mani[m].count, fin_apn);
     bool live = false;
-    const int rs = call_end(P, st, mode, obs, live);
+    const int rs = call_end(P, st, mode, obs, live, io.rep_stride);
     if (valid) {
       if (io.reward) io.reward[e] = live ? 1.0f : 0.0f;
       if (io.done) io.done[e] = (uint8_t)st.done;
