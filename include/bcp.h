@@ -124,8 +124,8 @@ typedef struct bcp_config {
   double contact_breaking_factor; /* gContactBreakingThreshold 0.02 */
   double max_friction;       /* 10 (combined friction clamp) */
   double warmstart_factor;   /* cached normal impulse x factor seeds the next solve;
-                                0.85 (btContactSolverInfo default) is what the
-                                README's stability known answer pins; 0 = off   */
+                                0.85 (btContactSolverInfo default): a calibrated
+                                choice, not pinned; 0 = off */
   int32_t gyro_term;         /* 1 */
   int32_t reserved1;
   double cart_ground_friction; /* >= 0: lateral friction of the cart AGAINST THE GROUND, when it differs from cart.friction
