@@ -325,7 +325,6 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   const bool valid = e_visit >= 0;
   const int e = valid ? e_visit : 0;
   const int64_t genv = P.env_id_offset + e;
-  const int width = 14 * P.R;
   T* rec = recs + (size_t)(valid ? e : 0) * rec_words;
   float* obs = (io.obs && valid) ? io.obs + (size_t)e * io.env_stride : nullptr;
   Env<T> st;

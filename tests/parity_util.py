@@ -103,7 +103,6 @@ def classify_step(env, ora, state: np.ndarray, actions: np.ndarray, rng=None, n_
     if fresh.any():
         dev_obs[fresh] = np.abs(obs[fresh].astype(np.float64) - obs_o[fresh].astype(np.float64)).reshape(int(fresh.sum()), -1).max(axis=1)
     dev = np.maximum(dev, dev_obs)
-    out = np.flatnonzero(dev > tol)
 
     # (A) the kernel's own discrete record against the oracle's
     cls = {}
