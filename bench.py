@@ -37,7 +37,8 @@ WORKLOAD = ("configs[2]: 65536 envs/GPU, continuous 2-D force, action_force=100,
 
 def workload_opts(args, **extra):
     return default_opts(action_force=100.0, initial_force=args.initial_force, action_repeats=args.repeats,
-                        steps_per_repeat=args.steps_per_repeat, cart_friction=args.cart_friction, **extra)
+                        steps_per_repeat=args.steps_per_repeat, cart_friction=args.cart_friction,
+                        no_carry_over_reset=args.no_carry_over_reset, reset_settle_cache=args.reset_settle_cache, **extra)
 
 
 # ---------------------------------------------------------------------------------------
@@ -114,20 +115,32 @@ def cpu_baseline(args, budget_s=None):
             "seconds": dt, "resets": resets}
 
 
-def secondary_workload(args):
-    """The workload where the pole is actually balanced on the cart (cart friction 1.0, R*S = 10, --initial-force=55: two-body
-    friction rows live, ~31 PGS iterations per substep), measured by this same script in a child process and reported BESIDE
-    the headline, never as it: SURVEY 8d asks for both workloads, each labelled."""
-    cmd = [sys.executable, os.path.abspath(__file__), "--cart-friction", "1.0", "--steps-per-repeat", "5", "--initial-force", "55",
-           "--steps", "10", "--warmup", "3", "--mix-calls", "60", "--envs", str(args.envs), "--no-secondary", "--cpu-budget", "6"]
+SECONDARY = {
+    # the workload where the pole is actually balanced on the cart (two-body friction rows live, ~31 PGS iterations per substep)
+    "upstream_style_workload": (["--cart-friction", "1.0", "--steps-per-repeat", "5", "--initial-force", "55", "--mix-calls", "60"],
+                                "cart friction 1.0, R*S = 10, --initial-force=55 (SURVEY 8d asks for both workloads, each labelled)"),
+    # configs[2] with the opt-in fast reset: a DEVIATION from pybullet's reset (the pending force and the contact caches are
+    # cleared, --no-carry-over-reset), under which the 100 settle substeps are the same computation in every env and are
+    # replayed from a per-handle cache (--reset-settle-cache): a reset costs its 30 push substeps.  Never the headline.
+    "fast_reset_workload": (["--no-carry-over-reset", "--reset-settle-cache"],
+                            "configs[2] with --no-carry-over-reset --reset-settle-cache: deviates from pybullet's reset semantics (opt-in)"),
+}
+
+
+def secondary_workload(args, name):
+    """A labelled workload measured by this same script in a child process and reported BESIDE the headline, never as it."""
+    extra, what = SECONDARY[name]
+    cmd = [sys.executable, os.path.abspath(__file__), *extra, "--steps", "10", "--warmup", "3", "--envs", str(args.envs),
+           "--no-secondary", "--cpu-budget", "6"]
     try:
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
         d = json.loads(r.stdout.strip().splitlines()[-1])
     except Exception as e:
         return {"unavailable": str(e)[:200]}
     keep = ("value", "unit", "ms_per_step", "steps", "live_fraction", "substeps_per_s", "kernel_ms_per_step", "e2e", "cpu_baseline")
-    out = {k: d.get(k) for k in keep}
-    out["config"] = {k: d["config"].get(k) for k in ("envs_per_gpu", "action_repeats", "steps_per_repeat", "initial_force", "cart_friction", "pipeline")}
+    out = {"what": what}
+    out.update({k: d.get(k) for k in keep})
+    out["config"] = {k: d["config"].get(k) for k in ("envs_per_gpu", "action_repeats", "steps_per_repeat", "initial_force", "cart_friction", "pipeline", "reset")}
     out["roofline"] = {k: d["roofline"].get(k) for k in ("bound", "whole_step_frac", "whole_step_achieved", "peak", "unit")}
     out["census"] = d.get("census")
     return out
@@ -507,6 +520,8 @@ def run_ours(args):
         "config": {"workload": WORKLOAD, "envs_per_gpu": n, "action_repeats": env.cfg.action_repeats,
                    "steps_per_repeat": env.cfg.steps_per_repeat, "initial_force": args.initial_force,
                    "cart_friction": env.cfg.cart.friction,
+                   "reset": "pybullet's (pending force and contact caches carried over; 100 settle + 30 push substeps)" if env.cfg.carry_over_reset
+                            else ("--no-carry-over-reset" + (" --reset-settle-cache (settle phase replayed: 30 push substeps per reset)" if env.cfg.reset_settle_cache else "")),
                    "termination": "angle/position/200-step rule on",
                    "auto_reset": "pipelined: a finished env runs its 130-substep reset R*S substeps per call; only env.steps "
                                  "actually taken are counted",
@@ -563,7 +578,8 @@ def run_ours(args):
     if not args.no_cpu_baseline and world == 1:
         out["cpu_baseline"] = cpu_baseline(args)
     if world == 1 and not args.no_secondary and args.cart_friction is None:
-        out["upstream_style_workload"] = secondary_workload(args)
+        for name in SECONDARY:
+            out[name] = secondary_workload(args, name)
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()
@@ -642,7 +658,9 @@ def main():
     ap.add_argument("--configs3-envs", type=int, default=1048576)
     ap.add_argument("--e2e-parts", type=int, default=2, help="the e2e host loop drives the batch as this many parts, multi-buffered")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-secondary", action="store_true", help="skip the upstream-style (friction, R*S = 10) workload reported beside the headline")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the labelled workloads reported beside the headline (upstream-style friction; fast reset)")
+    ap.add_argument("--no-carry-over-reset", action="store_true", help="reset() clears the pending force and the contact caches (deviation from pybullet)")
+    ap.add_argument("--reset-settle-cache", action="store_true", help="with --no-carry-over-reset: replay the settle phase from a per-handle cache")
     ap.add_argument("--cpu-budget", type=float, default=12.0, help="seconds of CPU work of the cpu_baseline sample")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

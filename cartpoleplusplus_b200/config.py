@@ -97,7 +97,7 @@ class BcpConfig(ctypes.Structure):
         ("max_friction", ctypes.c_double),
         ("warmstart_factor", ctypes.c_double),
         ("gyro_term", ctypes.c_int32),
-        ("reserved1", ctypes.c_int32),
+        ("reset_settle_cache", ctypes.c_int32),
         ("cart_ground_friction", ctypes.c_double),
     ]
 
@@ -198,6 +198,10 @@ def make_config(opts, discrete_actions: bool, num_envs: Optional[int] = None, dt
     c.force_frame = FRAME_WORLD if g("world_frame_force", False) else FRAME_LINK
     c.termination_enabled = 0 if g("no_termination", False) else 1
     c.carry_over_reset = 0 if g("no_carry_over_reset", False) else 1
+    c.reset_settle_cache = 1 if g("reset_settle_cache", False) else 0
+    if c.reset_settle_cache and c.carry_over_reset:
+        raise ValueError("--reset-settle-cache needs --no-carry-over-reset: with the pending force and the contact caches carried "
+                         "over (pybullet's behaviour) every env settles from a different state")
     ar = g("auto_reset", "off")
     if ar not in ("off", "pipelined"):
         raise ValueError(f"auto_reset must be 'off' or 'pipelined', got {ar!r}")

@@ -49,6 +49,8 @@ struct bcp_env {
   int* list = nullptr;   // compacted env indices for masked resets
   int* count = nullptr;
   double* staging = nullptr;  // canonical records for get/set_state
+  void* settled_f = nullptr;  // reset_settle_cache: the post-settle state record (Params::settled) ...
+  int* settled_i = nullptr;   // ... and its integer fields (the three point counts first)
   // Split pipeline.  The envs of a handle run as `cohorts` independent pipelines over disjoint env ranges, each on its
   // own stream: k_prep and the solve phase are both latency-bound, and one cohort's solve tail (a few warps iterating)
   // leaves most issue slots to the other cohort's k_prep.  Every per-env array is env-major, so a cohort's state,
@@ -132,6 +134,9 @@ int validate(const bcp_config* c) {
   if (c->solver_iterations < 1) return fail("bcp_create: solver_iterations must be >= 1");
   if (!(c->dt > 0)) return fail("bcp_create: dt must be > 0");
   if (!(c->cart.mass > 0) || !(c->pole.mass > 0)) return fail("bcp_create: cart and pole need positive mass");
+  if (c->reset_settle_cache && c->carry_over_reset)
+    return fail("bcp_create: reset_settle_cache needs carry_over_reset = 0 (with the pending force and the contact caches carried over, "
+                "every env settles from a different state)");
   return 0;
 }
 
@@ -176,6 +181,28 @@ int bcp_create(const bcp_config* cfg, bcp_env** out) {
     std::vector<int> init(N * bcp::NI, 0);
     for (size_t e = 0; e < N; ++e) init[e * bcp::NI + bcp::I_DONE] = 1;
     err = cudaMemcpy(h->idata, init.data(), init.size() * sizeof(int), cudaMemcpyHostToDevice);
+  }
+  if (cfg->reset_settle_cache && err == cudaSuccess) {
+    // the settle phase once, on a one-env scratch record, by the same reset program every env would run (teleport, caches and
+    // pending force cleared, settle_steps substeps, no pushes); its result is what every later reset starts its pushes from
+    const size_t fb1 = h->f64() ? bcp::Launch<double>::state_bytes(1) : bcp::Launch<float>::state_bytes(1);
+    A(&h->settled_f, fb1);
+    A((void**)&h->settled_i, (size_t)bcp::NI * sizeof(int));
+    if (err == cudaSuccess) {
+      if (h->f64()) {
+        bcp::Params<double> P1 = h->p64;
+        P1.num_envs = 1; P1.push_steps = 0;
+        err = bcp::Launch<double>::reset(P1, h->settled_f, h->settled_i, nullptr, nullptr, 1, nullptr, 0);
+      } else {
+        bcp::Params<float> P1 = h->p32;
+        P1.num_envs = 1; P1.push_steps = 0;
+        err = bcp::Launch<float>::reset(P1, h->settled_f, h->settled_i, nullptr, nullptr, 1, nullptr, 0);
+      }
+      if (err == cudaSuccess) err = cudaDeviceSynchronize();
+      h->p32.settled = static_cast<const float*>(h->settled_f);
+      h->p64.settled = static_cast<const double*>(h->settled_f);
+      h->p32.settled_cnt = h->p64.settled_cnt = h->settled_i + bcp::I_CNT;
+    }
   }
   // fp32 with enough envs to fill the machine: env.step runs as the split pipeline
   // (BCP_SPLIT=0/1 overrides; the one-launch fast kernel is the alternative)
@@ -246,6 +273,7 @@ int bcp_destroy(bcp_env* h) {
   DeviceGuard g(h->cfg.device_ordinal);
   cudaFree(h->fdata); cudaFree(h->idata); cudaFree(h->hist); cudaFree(h->header);
   cudaFree(h->reward_sum); cudaFree(h->list); cudaFree(h->count); cudaFree(h->staging);
+  cudaFree(h->settled_f); cudaFree(h->settled_i);
   if (h->hs.d_out) {
     cudaFree(h->hs.d_act); cudaFree(h->hs.d_out); cudaFree(h->hs.d_slab);
     cudaStreamDestroy(h->hs.copy); cudaEventDestroy(h->hs.ev_ready); cudaEventDestroy(h->hs.ev_copied); if (h->hs.ev_h2d) cudaEventDestroy(h->hs.ev_h2d);

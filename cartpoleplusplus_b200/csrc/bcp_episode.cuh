@@ -5,6 +5,9 @@ namespace bcp {
 
 // teleport of reset(): p.resetBasePositionAndOrientation x2, bullet_cartpole.py:319-320
 // (zeroes the base velocities; the pair caches and the pending force survive).
+// With the settle cache (Params::settled; only in the --no-carry-over-reset mode, where the 100 settle substeps start from
+// the same state in every env and are therefore the same computation) the env takes the cached post-settle state instead:
+// bodies and point counts here, the points themselves in settled_points() (the split pipeline copies the blocks in HBM).
 template <typename T> BCP_HD void reset_begin(const Params<T>& P, Env<T>& st) {
   st.steps = 0;  // :315
   st.done = 0;   // :316
@@ -18,7 +21,31 @@ template <typename T> BCP_HD void reset_begin(const Params<T>& P, Env<T>& st) {
   if (!P.carry_over) {
     for (int i = 0; i < 3; ++i) { st.pend_f[i] = st.pend_t[i] = 0; st.mani[i].count = 0; }
   }
+  if (P.settled) {
+    const T* c = P.settled + BCP_S_CART;
+    const T* q = P.settled + BCP_S_POLE;
+    for (int i = 0; i < 3; ++i) {
+      st.cart.x[i] = c[i]; st.cart.v[i] = c[7 + i]; st.cart.w[i] = c[10 + i];
+      st.pole.x[i] = q[i]; st.pole.v[i] = q[7 + i]; st.pole.w[i] = q[10 + i];
+      st.pend_f[i] = P.settled[BCP_S_PEND_F + i]; st.pend_t[i] = P.settled[BCP_S_PEND_T + i];
+      st.mani[i].count = P.settled_cnt[i];
+    }
+    for (int i = 0; i < 4; ++i) { st.cart.q[i] = c[3 + i]; st.pole.q[i] = q[3 + i]; }
+  }
 }
+template <typename T> BCP_HD void settled_points(const Params<T>& P, Env<T>& st) {
+  if (!P.settled) return;
+  for (int m = 0; m < 3; ++m)
+    for (int k = 0; k < 4; ++k) {
+      const T* q = P.settled + BCP_S_MANI + m * BCP_MANI_STRIDE + k * BCP_MANI_POINT;
+      MPoint<T>& p = st.mani[m].p[k];
+      for (int i = 0; i < 3; ++i) { p.la[i] = q[i]; p.lb[i] = q[3 + i]; p.n[i] = q[6 + i]; }
+      p.dist = q[9];
+      p.imp = q[10];
+    }
+}
+// substeps of a reset that are actually run: the settle loop is skipped when its result is cached
+template <typename T> BCP_HD int reset_settle_steps(const Params<T>& P) { return P.settled ? 0 : P.settle_steps; }
 
 // the k-th of the 30 initial pushes: bump_cart -> random_force_in_plane, :348-359
 template <typename T> BCP_HD void push_force(const Params<T>& P, int64_t genv, int episode, int k, T& ts, T& tc) {
@@ -44,9 +71,10 @@ template <typename T, typename STEP>
 BCP_HD void env_reset(const Params<T>& P, Env<T>& st, int64_t genv, const STEP& sub, bool on) {
   if (on) {
     reset_begin(P, st);
+    settled_points(P, st);
     st.reset_left = 0;
   }
-  for (int k = 0; k < P.settle_steps; ++k) sub(P, st, on);  // :326-327
+  for (int k = 0; k < reset_settle_steps(P); ++k) sub(P, st, on);  // :326-327
   T ts = 0, tc = 1;
   if (on && P.theta_mode == BCP_THETA_PER_RESET) push_force(P, genv, st.episode, 0, ts, tc);
   for (int k = 0; k < P.push_steps; ++k) {  // :329-332
@@ -87,14 +115,17 @@ template <typename T> BCP_HD void action_force(const Params<T>& P, int a_disc, f
 //   reset finishes: observation bootstrap (:338-339) at the end of that call, FRESH
 enum { MODE_IDLE = 0, MODE_LIVE = 1, MODE_RESET = 2, MODE_FRESH = 3 };
 
-template <typename T> BCP_HD int call_begin(const Params<T>& P, Env<T>& st, bool valid) {
+// points: the caller holds the manifold points in `st` (one-launch programs); the split pipeline keeps them in HBM and copies
+// the cached blocks itself when a reset begins (k_prep)
+template <typename T> BCP_HD int call_begin(const Params<T>& P, Env<T>& st, bool valid, bool points = true) {
   if (!valid) return MODE_IDLE;
   if (!st.done) return MODE_LIVE;
   if (P.auto_reset != BCP_AUTO_RESET_PIPELINED) return MODE_IDLE;
   if (st.reset_left == 0) {  // episode ended in an earlier call: the reset starts
     reset_begin(P, st);
+    if (points) settled_points(P, st);
     st.done = 1;
-    st.reset_left = P.settle_steps + P.push_steps;
+    st.reset_left = reset_settle_steps(P) + P.push_steps;
     if (st.reset_left == 0) { st.done = 0; st.episode += 1; return MODE_FRESH; }
   }
   return MODE_RESET;
@@ -107,7 +138,7 @@ template <typename T> BCP_HD void post_substep(const Params<T>& P, Env<T>& st, i
   if (mode == MODE_LIVE) {
     apply_cart_force(P, st, fx, fy);
   } else if (mode == MODE_RESET && st.reset_left > 0) {
-    const int k = (P.settle_steps + P.push_steps) - st.reset_left - P.settle_steps;  // push index
+    const int k = P.push_steps - st.reset_left;  // push index; < 0 while settling (reset_left counts settle + push substeps still to run)
     if (k >= 0) {
       T ts, tc;
       push_force(P, genv, st.episode, (P.theta_mode == BCP_THETA_PER_SUBSTEP) ? k : 0, ts, tc);

@@ -362,7 +362,18 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
         }
     }
   }
-  if (s_fin < 0) mode = call_begin(P, st, valid);
+  if (s_fin < 0) {
+    const bool idle_done = valid && st.done && st.reset_left == 0;
+    mode = call_begin(P, st, valid, false);
+    if (P.settled && idle_done && mode != MODE_IDLE) {  // a reset began on the cached post-settle state: its manifold blocks too
+      for (int m = 0; m < 3; ++m)
+        if (st.mani[m].count > 0) {
+          T blk[BCP_MANI_STRIDE];
+          copy16(P.settled + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
+          store16(f + (size_t)e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
+        }
+    }
+  }
   const bool fin = s_fin >= 0 && valid && substep_on(mode, st);
   if (fin) finish_bodies(P, st, fin_dvel);
   if (s_fin >= 0 && valid) {

@@ -52,6 +52,12 @@ template <typename T> struct Params {
   // fast-mode row column layout (bcp_fast.cuh): per pair, rows per contact (1 normal +
   // friction rows when the pair has friction) and the first word of the pair's rows
   int rows_per_contact[3], row_base[3], col_words;
+  // --no-carry-over-reset with the settle cache (bcp_config.reset_settle_cache): the state every env is in after the
+  // teleport and the 100 settle substeps - identical for all of them when reset() clears the pending force and the contact
+  // caches - computed once per handle: one state record (layout of bcp_state.cuh: bodies, pending force, 3 x 4 manifold
+  // points) and its three point counts, in device memory.  nullptr: every reset runs its settle substeps.
+  const T* settled;
+  const int* settled_cnt;
 };
 
 // ---- host-side conversion (plain host functions; never called from device code) ----
@@ -124,6 +130,8 @@ template <typename T> inline Params<T> make_params(const bcp_config& c) {
   p.num_envs = c.num_envs;
   p.env_id_offset = c.env_id_offset;
   p.seed = c.seed;
+  p.settled = nullptr;
+  p.settled_cnt = nullptr;
   p.col_words = 0;
   for (int m = 0; m < 3; ++m) {
     p.rows_per_contact[m] = (p.mu[m] != T(0.0)) ? 1 + c.friction_dirs : 1;

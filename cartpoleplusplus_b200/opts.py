@@ -52,6 +52,9 @@ def add_opts(parser: argparse.ArgumentParser) -> None:
                         help="override cart.urdf lateral_friction (fork: 0.0)")
     parser.add_argument("--no-carry-over-reset", action="store_true",
                         help="clear the pending force and contact caches on reset (deviation from pybullet)")
+    parser.add_argument("--reset-settle-cache", action="store_true",
+                        help="with --no-carry-over-reset: compute the 100 settle substeps of reset() once and replay their result "
+                             "(exact in that mode: every env settles from the same state)")
     parser.add_argument("--model-dir", type=str, default=None, help="directory with ground/cart/pole .urdf")
     parser.add_argument("--cart-model", type=str, default="cart", choices=["cart", "double_cart"],
                         help="cart: models/cart.urdf (bullet_cartpole.py:155); double_cart: the fork's compound cart of "

@@ -127,7 +127,9 @@ typedef struct bcp_config {
                                 0.85 (btContactSolverInfo default): a calibrated
                                 choice, not pinned; 0 = off */
   int32_t gyro_term;         /* 1 */
-  int32_t reserved1;
+  int32_t reset_settle_cache; /* 1 (only with carry_over_reset = 0): the 100 settle substeps of reset() (:326-327), which then
+                                 start from the same state in every env, are computed once per handle and their result is
+                                 replayed; a reset costs its 30 push substeps.  0: every reset runs them (the reference)    */
   double cart_ground_friction; /* >= 0: lateral friction of the cart AGAINST THE GROUND, when it differs from cart.friction
                                   (what the pole touches): the fork's compound cart, models/double_cart_1.urdf:15-80 - upper half
                                   1.0, lower half 0.0.  < 0: cart.friction serves both pairs (cart.urdf)                       */
