@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
       if (on) {
         Manifold<T>& mf = F.mf;
         mf.count = st.mani[m].count;
-        load_manifold<T>(f, e, m, mf);
+        load_manifold_mem<T>(f, e, m, mf);
         if (fin) {
 #pragma unroll
           for (int j = 0; j < 4; ++j)
@@ -415,7 +415,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
         }
         setup_pair<T, FRICTION>(P, m, gbox, F, C, rec, L);
         st.mani[m].count = mf.count;
-        store_manifold<T>(f, e, m, mf);
+        store_manifold_mem<T>(f, e, m, mf);
       } else if (fin) {
         finish_impulses(f, e, m, st.mani[m].count, fin_apn);
       }

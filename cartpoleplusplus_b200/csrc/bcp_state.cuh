@@ -115,6 +115,35 @@ template <typename T> BCP_HD void store_manifold(T* f, size_t e, int m, const Ma
   }
   store16(f + e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE, blk, BCP_MANI_STRIDE);
 }
+// The same for a manifold that lives in addressable memory (k_prep's shared-memory frame): the four points of Manifold<T> are
+// 44 contiguous scalars in the record block's own order (la3, lb3, n3, dist, imp per point), so the block moves as eleven
+// 16-byte pieces without a staging array and without per-field unpacking.  Points past `count` carry whatever the block held
+// on the way in (never read) and go out as zeros, like store_manifold.
+static_assert(sizeof(MPoint<float>) == BCP_MANI_POINT * sizeof(float) && sizeof(MPoint<double>) == BCP_MANI_POINT * sizeof(double),
+              "MPoint is the record's point layout");
+template <typename T> BCP_HD void load_manifold_mem(const T* f, size_t e, int m, Manifold<T>& mf) {
+  if (mf.count <= 0) return;
+  const T* src = f + e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE;
+  T* dst = &mf.p[0].la[0];
+  constexpr int W = 16 / (int)sizeof(T);
+  for (int i = 0; i < BCP_MANI_STRIDE; i += W) {
+    T v[W];
+    copy16(src + i, v, W);
+    for (int k = 0; k < W; ++k) dst[i + k] = v[k];
+  }
+}
+template <typename T> BCP_HD void store_manifold_mem(T* f, size_t e, int m, const Manifold<T>& mf) {
+  if (mf.count <= 0) return;
+  T* dst = f + e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE;
+  const T* src = &mf.p[0].la[0];
+  const int live = mf.count * BCP_MANI_POINT;
+  constexpr int W = 16 / (int)sizeof(T);
+  for (int i = 0; i < BCP_MANI_STRIDE; i += W) {
+    T v[W];
+    for (int k = 0; k < W; ++k) v[k] = (i + k < live) ? src[i + k] : T(0);
+    store16(dst + i, v, W);
+  }
+}
 template <typename T> BCP_HD void store_env_core(T* f, int* id, size_t e, const Env<T>& st) {
   T* r = f + e * NF;
   int* ir = id + e * NI;
