@@ -293,10 +293,24 @@ __device__ __forceinline__ int visit(const VisitOrder& vo, int i, int N) {
 
 // a finished solve's normal impulses into the cached points of pair m, in place in the record
 // (the only thing a finish changes in a manifold)
+// slot j of pair m out of the 12 applied impulses, and one of three counts, by comparison: an index that is only known at
+// run time (m of the rolled pair loop) would put the whole array - and the Env record with it - into local memory
+template <typename T> BCP_HD T apn_of(const T* apn, int m, int j) {
+  return m == BCP_PAIR_GROUND_CART ? apn[SLOT_GC + j] : (m == BCP_PAIR_CART_POLE ? apn[SLOT_CP + j] : apn[SLOT_GP + j]);
+}
+template <typename T> BCP_HD int count_of(const Env<T>& st, int m) {
+  return m == 0 ? st.mani[0].count : (m == 1 ? st.mani[1].count : st.mani[2].count);
+}
+template <typename T> BCP_HD void set_count(Env<T>& st, int m, int c) {
+  if (m == 0) st.mani[0].count = c;
+  else if (m == 1) st.mani[1].count = c;
+  else st.mani[2].count = c;
+}
 template <typename T> BCP_HD void finish_impulses(T* f, size_t e, int m, int count, const T* fin_apn) {
   T* blk = f + e * NF + BCP_S_MANI + m * BCP_MANI_STRIDE;
+#pragma unroll
   for (int j = 0; j < 4; ++j)
-    if (j < count) blk[j * BCP_MANI_POINT + 10] = fin_apn[slot_of_pair(m) + j];
+    if (j < count) blk[j * BCP_MANI_POINT + 10] = apn_of(fin_apn, m, j);
 }
 template <typename T> BCP_HD int queue_meta(const Env<T>& st) {
   return st.mani[0].count | (st.mani[1].count << 8) | (st.mani[2].count << 16);
@@ -366,6 +380,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     const bool idle_done = valid && st.done && st.reset_left == 0;
     mode = call_begin(P, st, valid, false);
     if (P.settled && idle_done && mode != MODE_IDLE) {  // a reset began on the cached post-settle state: its manifold blocks too
+#pragma unroll
       for (int m = 0; m < 3; ++m)
         if (st.mani[m].count > 0) {
           T blk[BCP_MANI_STRIDE];
@@ -388,6 +403,9 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     post_substep(P, st, genv, mode, fx, fy);
     if ((s_fin + 1) % P.S == 0 && mode == MODE_LIVE && obs) write_obs(st, obs + io.rep_stride * (s_fin / P.S));  // :237
   }
+  bool q_on = false, q_gen = false, q_long = false;  // the env's queue entry (written at the end of the kernel)
+  unsigned ml = 0, ms = 0, mg = 0;
+  int bl = 0, bs = 0, bg = 0;
   if (s_set >= 0) {
     const bool on = valid && substep_on(mode, st);
     if (!on) last_iters = 0;
@@ -406,48 +424,44 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
       BCP_WARP_SYNC();
       if (on) {
         Manifold<T>& mf = F.mf;
-        mf.count = st.mani[m].count;
+        mf.count = count_of(st, m);
         load_manifold_mem<T>(f, e, m, mf);
         if (fin) {
 #pragma unroll
           for (int j = 0; j < 4; ++j)
-            if (j < mf.count) mf.p[j].imp = fin_apn[slot_of_pair(m) + j];
+            if (j < mf.count) mf.p[j].imp = apn_of(fin_apn, m, j);
         }
         setup_pair<T, FRICTION>(P, m, gbox, F, C, rec, L);
-        st.mani[m].count = mf.count;
+        set_count(st, m, mf.count);
         store_manifold_mem<T>(f, e, m, mf);
       } else if (fin) {
-        finish_impulses(f, e, m, st.mani[m].count, fin_apn);
+        finish_impulses(f, e, m, count_of(st, m), fin_apn);
       }
     }
     BCP_WARP_SYNC();
-    if (on) setup_end(P, st, C, rec);
-    // queue the env: one atomic per warp and bin
-    // with the impulse-space solver on the main queue, an env in a regime it does not cover goes to
+    // queue the env: one atomic per warp and bin, ISSUED here and used at the very end of the kernel - the round trip of a
+    // contended atomic (a microsecond) then runs beside the stores of setup_end and of the state core instead of stalling
+    // the whole warp in front of them (it was 8 % of the kernel's stall samples).
+    // With the impulse-space solver on the main queue, an env in a regime it does not cover goes to
     // the generic queue (second half of `queue`, second counter block)
-    const bool generic = on && use_lam &&
+    q_on = on;
+    q_gen = on && use_lam &&
         lam_mode_of(st.mani[BCP_PAIR_GROUND_CART].count, st.mani[BCP_PAIR_CART_POLE].count, st.mani[BCP_PAIR_GROUND_POLE].count) == LAM_NONE;
-    const bool is_long = on && !generic && last_iters >= kLongIters;
-    const unsigned ml = __ballot_sync(0xffffffffu, is_long), ms = __ballot_sync(0xffffffffu, on && !is_long && !generic);
-    const unsigned mg = __ballot_sync(0xffffffffu, generic);
-    const int lane = threadIdx.x & 31;
-    int bl = 0, bs = 0, bg = 0;
-    if (lane == 0) {
+    q_long = on && !q_gen && last_iters >= kLongIters;
+    ml = __ballot_sync(0xffffffffu, q_long);
+    ms = __ballot_sync(0xffffffffu, on && !q_long && !q_gen);
+    mg = __ballot_sync(0xffffffffu, q_gen);
+    if ((threadIdx.x & 31) == 0) {
       if (ml) bl = atomicAdd(&qc_set[Q_LONG], __popc(ml));
       if (ms) bs = atomicAdd(&qc_set[Q_SHORT], __popc(ms));
       if (mg) bg = atomicAdd(&qc_set[Q_WORDS + Q_SHORT], __popc(mg));
     }
-    bl = __shfl_sync(0xffffffffu, bl, 0);
-    bs = __shfl_sync(0xffffffffu, bs, 0);
-    bg = __shfl_sync(0xffffffffu, bg, 0);
-    const unsigned lt = (1u << lane) - 1;
-    // entry = env id + its three contact counts (the solver sizes its copy without the record)
-    const int2 entry = make_int2(e, queue_meta(st));
-    if (is_long) queue[bl + __popc(ml & lt)] = entry;
-    else if (generic) queue[N + N - 1 - (bg + __popc(mg & lt))] = entry;
-    else if (on) queue[N - 1 - (bs + __popc(ms & lt))] = entry;
+    if (on) setup_end(P, st, C, rec);
   } else {  // the call closes: steps / done / reward (:239-260), outputs, episode statistics
-    if (fin) for (int m = 0; m < 3; ++m) finish_impulses(f, e, m, st.mani[m].count, fin_apn);
+    if (fin) {
+#pragma unroll
+      for (int m = 0; m < 3; ++m) finish_impulses(f, e, m, st.mani[m].count, fin_apn);
+    }
     bool live = false;
     const int rs = call_end(P, st, mode, obs, live, io.rep_stride);
     if (valid) {
@@ -481,6 +495,18 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   if (valid) {
     store_env_core<T>(f, id, e, st);
     id[(size_t)e * NI + I_MODE] = mode;
+  }
+  if (s_set >= 0) {  // the queue entry, at the slots the atomics above handed out
+    const int lane = threadIdx.x & 31;
+    bl = __shfl_sync(0xffffffffu, bl, 0);
+    bs = __shfl_sync(0xffffffffu, bs, 0);
+    bg = __shfl_sync(0xffffffffu, bg, 0);
+    const unsigned lt = (1u << lane) - 1;
+    // entry = env id + its three contact counts (the solver sizes its copy without the record)
+    const int2 entry = make_int2(e, queue_meta(st));
+    if (q_long) queue[bl + __popc(ml & lt)] = entry;
+    else if (q_gen) queue[N + N - 1 - (bg + __popc(mg & lt))] = entry;
+    else if (q_on) queue[N - 1 - (bs + __popc(ms & lt))] = entry;
   }
 }
 

@@ -90,6 +90,19 @@ def main():
     print("-- by function (samples %, warp-instructions executed)")
     for k, v in by_func.most_common(30):
         print(f"{100.0 * v / total:6.1f} %  {inst_by_func[k]:>10}  {k[0]}:{k[1]}")
+    # where each kind of stall sits: the per-instruction stall columns of the source page, by line
+    for col in ("stall_long_sb", "stall_no_inst", "stall_wait", "stall_short_sb"):
+        if col not in cols:
+            continue
+        by = collections.Counter()
+        for r in inst:
+            by[where.get(int(r[0], 16) - base, ("?", 0))] += int(r[cols[col]] or 0)
+        tot = sum(by.values())
+        if not tot:
+            continue
+        print(f"-- {col}: {tot} samples ({100.0 * tot / max(total, 1):.1f} % of all); top lines")
+        for (f, ln), n in by.most_common(8):
+            print(f"  {100.0 * n / tot:5.1f} %  {os.path.basename(f)}:{ln}")
     print("-- hottest lines")
     for k, v in by_line.most_common(25):
         print(f"{100.0 * v / total:6.1f} %  {k[0]}:{k[1]}")
