@@ -80,3 +80,30 @@ def test_trajectories_do_not_depend_on_the_sharding(built, N):
             st = whole.get_state()
             for i, h in enumerate(halves):
                 h.set_state(st[i * (N // 2):(i + 1) * (N // 2)])
+
+
+@pytest.mark.parametrize("n,cohorts", [(40037, 3), (5000, 4), (70001, 8)])
+def test_cohort_split_of_an_odd_batch_is_invisible(built, monkeypatch, n, cohorts):
+    """A batch whose size is no multiple of anything, run as one pipeline and as `cohorts` (BCP_COHORTS; the cohort bases
+    are rounded to whole blocks, the last cohort takes the rest): same outputs bit for bit over env.steps with resets, and
+    through bcp_step_host."""
+    monkeypatch.setenv("BCP_COHORTS", "1")
+    one = _env(n, initial_force=55.0, auto_reset="pipelined")
+    monkeypatch.setenv("BCP_COHORTS", str(cohorts))
+    many = _env(n, initial_force=55.0, auto_reset="pipelined")
+    assert torch.equal(one.reset(), many.reset())
+    for e in (one, many):
+        e.rollout_random(30)  # into the mix of live / resetting envs
+    assert np.array_equal(one.get_state(), many.get_state())
+    g = torch.Generator(device="cuda")
+    g.manual_seed(11)
+    for t in range(6):
+        a = torch.rand((n, 2), device="cuda", generator=g) * 2 - 1
+        if t < 4:
+            ra, rb = one.step(a), many.step(a)
+        else:
+            ha = a.cpu().pin_memory()
+            ra, rb = one.step_host(ha), many.step_host(ha)
+        for x, y in zip(ra[:3], rb[:3]):
+            assert torch.equal(torch.as_tensor(x), torch.as_tensor(y)), t
+    assert np.array_equal(one.get_state(), many.get_state())
