@@ -58,6 +58,8 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   if (err != cudaSuccess) return err;
   err = allow_smem(k_solve_lam<float, FRICTION>, L.smem);
   if (err != cudaSuccess) return err;
+  err = allow_smem(k_solve_lam_once<float, FRICTION>, L.smem);
+  if (err != cudaSuccess) return err;
   // Impulse-space solver (bcp_lambda.cuh) on the main queue.  It shortens the dependent chain of an
   // iteration, which is what bounds the solve phase while a launch is about one wave of envs
   // (measured on B200: +6..7 % env-steps/s at 32 768 and 65 536 envs, equal at 131 072); beyond
@@ -68,6 +70,11 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   if (handoff < 0) {
     const char* he = getenv("BCP_HANDOFF");
     handoff = he ? atoi(he) : 8;  // iterations after which a solve moves to k_solve_tail (0: never)
+  }
+  static int lam_once = -1;
+  if (lam_once < 0) {
+    const char* lo = getenv("BCP_LAM_ONCE");
+    lam_once = lo ? atoi(lo) : 1;
   }
   int tail_grid = (N + kBlock - 1) / kBlock;
   if (tail_grid > 2 * 148) tail_grid = 2 * 148;
@@ -134,8 +141,12 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
           k_solve<float, FRICTION><<<gen_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride, fetch_min);
           cudaEventRecord(b.ev_gen, b.side);
         }
-        k_solve_lam<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc, col_stride, fetch_min,
-                                                                          b.cont, reinterpret_cast<int4*>(b.contm), handoff);
+        if (handoff > 0 && lam_once)  // at most `handoff` iterations per solve here: one chunk of the queue per warp, no pool
+          k_solve_lam_once<float, FRICTION><<<(N + L.block - 1) / L.block, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc,
+                                                                                                 col_stride, b.cont, reinterpret_cast<int4*>(b.contm), handoff);
+        else
+          k_solve_lam<float, FRICTION><<<solve_grid, L.block, L.smem, s>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue), qc, col_stride, fetch_min,
+                                                                            b.cont, reinterpret_cast<int4*>(b.contm), handoff);
         if (handoff > 0) {
           k_solve_tail<float, FRICTION><<<tail_grid, kBlock, 0, s>>>(P, b.recs, rec_words, qc, b.cont, reinterpret_cast<const int4*>(b.contm));
           if (launches) ++*launches;

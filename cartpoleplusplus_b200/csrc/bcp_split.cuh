@@ -593,7 +593,13 @@ template <typename T> struct PoolFeed {
       meta = q.y;
     }
     staged = __ballot_sync(FULL, idx >= 0);
-    unsigned taken = staged;
+    stage(staged, lane, env, meta, recs, rec_words, smem, warp_base, col_stride);
+    return env;
+  }
+  // the whole warp issues the record -> column copies of the lanes in `taken` (lane l: env / meta of its own record)
+  __device__ __forceinline__ void stage(unsigned taken, int lane, int env, int meta, const T* __restrict__ recs, int rec_words, T* smem,
+                                        int warp_base, int col_stride) {
+    const unsigned FULL = 0xffffffffu;
     while (taken) {
       const int src = __ffs(taken) - 1;
       taken &= taken - 1;
@@ -608,7 +614,6 @@ template <typename T> struct PoolFeed {
         }
       }
     }
-    return env;
   }
 };
 
@@ -777,6 +782,99 @@ __global__ void __launch_bounds__(kBlock, 2) k_solve_lam(const __grid_constant__
 #pragma unroll
       for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, still ? cnt[m] : 0);
     }
+  }
+}
+// k_solve_lam without the pool: warp w takes queue entries 32 w .. 32 w + 31, once.  With the hand-off to k_solve_tail a
+// solve spends at most `handoff_it` iterations here, so there is no long tail for a refill to hide - and the launch has
+// about one lane per queued env anyway -: the pool's slice atomics, refill rounds and per-round retire code were a third of
+// k_solve_lam's instructions and 45 % of its stall samples (profiles/r2_k_solve_lam_by_source.txt).  Same staged
+// record -> column copy, same per-lane arithmetic (build, rounds, finish, hand-off), so the results are the pool's bit for
+// bit; a lane that converges early waits for its warp (at most handoff_it rounds) and all finishes run together.
+template <typename T, bool FRICTION>
+__global__ void __launch_bounds__(kBlock, 2) k_solve_lam_once(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
+                                                       const int2* __restrict__ queue, int* __restrict__ qc, int col_stride,
+                                                       T* __restrict__ cont, int4* __restrict__ contm, int handoff_it) {
+  const unsigned FULL = 0xffffffffu;
+  T* const smem = reinterpret_cast<T*>(bcp_smem);
+  const int lane = threadIdx.x & 31, warp_base = threadIdx.x - lane;
+  T* const col = smem + (size_t)threadIdx.x * col_stride;
+  const SolveLayout L = solve_layout(P);
+  const int N = P.num_envs;
+  const unsigned lt = (1u << lane) - 1;
+  PoolFeed<T> feed;  // its piece table and queue geometry; nothing is fetched through it
+  feed.init(L, lane, rec_words, qc, N);
+  SolveScale<T> S;
+  {
+    SolveRegs<T> R0;
+    solve_consts(P, R0, S);
+  }
+  const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+  const T res_thr = P.residual_thr;
+  const int max_it = P.solver_iterations;
+  const int warps = gridDim.x * (blockDim.x >> 5);
+  for (int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w * 32 < feed.total; w += warps) {
+    const int idx = w * 32 + lane;
+    const bool have = idx < feed.total;
+    int env = 0, meta = 0;
+    if (have) {
+      const int2 q = queue[idx < feed.n_long ? idx : N - 1 - (idx - feed.n_long)];
+      env = q.x;
+      meta = q.y;
+    }
+    feed.stage(__ballot_sync(FULL, have), lane, env, meta, recs, rec_words, smem, warp_base, col_stride);
+    cp_async_wait_all();
+    __syncwarp();
+    T* const rec = recs + (size_t)env * rec_words;
+    LamSys<T> Sy;
+    int lmode = LAM_NONE, it = 0;
+    int cnt[3] = {0, 0, 0}, mx[3];
+    if (have) {
+      SolveRegs<T> R;
+      solve_load(col, S, cnt, R);  // counts and warm-start impulses
+      lmode = lam_mode_of(cnt[0], cnt[1], cnt[2]);
+      if (lmode == LAM_STACK) lam_build_stack<true>(P, col + REC_ROWS, L, R.apn, Sy);
+      else lam_build_split<true, FRICTION>(P, col + REC_ROWS, L, R.apn, Sy);
+    }
+#pragma unroll
+    for (int m = 0; m < 3; ++m) mx[m] = __reduce_max_sync(FULL, have ? cnt[m] : 0);
+    bool open = have, conv = false;
+    while (__any_sync(FULL, open)) {
+      if (open) {
+        const T lsr = lmode == LAM_STACK ? lam_round_stack(P, mx[BCP_PAIR_CART_POLE], mx[BCP_PAIR_GROUND_CART], Sy)
+                                         : lam_round_split<FRICTION>(P, fr, mx[BCP_PAIR_GROUND_POLE], mx[BCP_PAIR_GROUND_CART], Sy);
+        it++;
+        conv = lsr <= res_thr || it >= max_it;
+        if (conv || (handoff_it > 0 && it >= handoff_it)) open = false;
+      }
+    }
+    // still running after handoff_it iterations: the system goes to the continuation buffer (STACK entries from the
+    // front, SPLIT from the back) and k_solve_tail
+    const bool hand = have && !conv;
+    const unsigned hm = __ballot_sync(FULL, hand);
+    if (hm) {
+      const unsigned hs = __ballot_sync(FULL, hand && lmode == LAM_STACK), hp = hm & ~hs;
+      int b0 = 0, b1 = 0;
+      if (lane == 0) {
+        if (hs) b0 = atomicAdd(&qc[2 * Q_WORDS + 0], __popc(hs));
+        if (hp) b1 = atomicAdd(&qc[2 * Q_WORDS + 1], __popc(hp));
+      }
+      b0 = __shfl_sync(FULL, b0, 0);
+      b1 = __shfl_sync(FULL, b1, 0);
+      if (hand) {
+        const int slot = lmode == LAM_STACK ? b0 + __popc(hs & lt) : N - 1 - (b1 + __popc(hp & lt));
+        lam_store(cont, N, slot, Sy);
+        contm[slot] = make_int4(env, it, cnt[0] | (cnt[1] << 8) | (cnt[2] << 16), lmode);
+      }
+    }
+    if (have && conv) {  // bodies' deltas from the impulses and the rows still in the column
+      SolveRegs<T> R;
+      R.cart.invM = P.cart.inv_mass;
+      R.pole.invM = P.pole.inv_mass;
+      if (lmode == LAM_STACK) lam_finish_stack<true>(P, col + REC_ROWS, L, Sy, R);
+      else lam_finish_split<true, FRICTION>(P, col + REC_ROWS, L, Sy, R);
+      solve_end(rec, S, it, R);
+    }
+    __syncwarp();  // the columns are reused by the warp's next chunk
   }
 }
 // The solves k_solve_lam handed off, one per lane, 32 consecutive continuation slots per warp (all
