@@ -60,6 +60,8 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   if (err != cudaSuccess) return err;
   err = allow_smem(k_solve_lam_once<float, FRICTION>, L.smem);
   if (err != cudaSuccess) return err;
+  err = allow_smem(k_solve_gen_once<float, FRICTION>, L.smem);
+  if (err != cudaSuccess) return err;
   // Impulse-space solver (bcp_lambda.cuh) on the main queue.  It shortens the dependent chain of an
   // iteration, which is what bounds the solve phase while a launch is about one wave of envs
   // (measured on B200: +6..7 % env-steps/s at 32 768 and 65 536 envs, equal at 131 072); beyond
@@ -70,6 +72,11 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   if (handoff < 0) {
     const char* he = getenv("BCP_HANDOFF");
     handoff = he ? atoi(he) : 8;  // iterations after which a solve moves to k_solve_tail (0: never)
+  }
+  static int lam_gen = -1;
+  if (lam_gen < 0) {
+    const char* lg = getenv("BCP_LAM_GEN");
+    lam_gen = lg ? atoi(lg) : 1;
   }
   static int lam_once = -1;
   if (lam_once < 0) {
@@ -138,7 +145,10 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
         if (side) {
           cudaEventRecord(b.ev_prep, s);
           cudaStreamWaitEvent(b.side, b.ev_prep, 0);
-          k_solve<float, FRICTION><<<gen_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride, fetch_min);
+          if (lam_gen)  // impulse space for these too: half the latency per iteration of solves that mostly run all 50
+            k_solve_gen_once<float, FRICTION><<<gen_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride);
+          else
+            k_solve<float, FRICTION><<<gen_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride, fetch_min);
           cudaEventRecord(b.ev_gen, b.side);
         }
         if (handoff > 0 && lam_once)  // at most `handoff` iterations per solve here: one chunk of the queue per warp, no pool

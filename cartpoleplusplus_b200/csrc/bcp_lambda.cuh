@@ -304,4 +304,192 @@ BCP_HD void lam_finish_split(const Params<T>& P, const T* colp, const SolveLayou
   }
 }
 
+// ---- GEN: the regime neither STACK nor SPLIT covers - the pole touches the cart AND the ground ----
+// Up to 20 rows that all couple (cart: cart-pole + ground-cart rows; pole: cart-pole + ground-pole rows and their friction
+// pairs): the 162 entries of the Delassus matrix that are not structurally zero (ground-cart and ground-pole rows share no
+// body) do not leave room for anything else in a lane's registers, which is fine for what this regime is - a few dozen envs
+// per launch (a pole leaning between cart and ground) that never reach the residual threshold and whose 50 row-space
+// iterations on the side stream were the longest chain of the whole solve phase.  In impulse space the chain from row to
+// row is the same 6 instructions as in STACK / SPLIT.
+//   pole block  (rows 0..11: ground-pole normals, then friction pair 4 + 2c / 5 + 2c)   Ap  12 x 12 packed
+//   cart-pole   (rows 12..15)  Ac 4 x 4 packed        ground-cart (rows 16..19)  Ag 4 x 4 packed
+//   Acg[i * 4 + k]  cart-pole i x ground-cart k (through the cart)      Acp[i * 12 + k]  cart-pole i x pole-block k (the pole)
+template <typename T> struct LamGen {
+  T Ap[78], Ac[10], Ag[10], Acg[16], Acp[48];
+  T lam[20], res[20], invd[20];
+};
+template <bool SMEM, bool FRICTION, typename T>
+BCP_HD void lam_build_gen(const Params<T>& P, const T* colp, const SolveLayout& L, const T* apn, LamGen<T>& S) {
+  const T* const gp = colp + L.base[BCP_PAIR_GROUND_POLE];
+  const T* const cp = colp + L.base[BCP_PAIR_CART_POLE];
+  const T* const gc = colp + L.base[BCP_PAIR_GROUND_CART];
+  const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+  const T* const fgp = colp + (fr ? L.fbase[BCP_PAIR_GROUND_POLE] : 0);
+  const T imc = P.cart.inv_mass, imp = P.pole.inv_mass;
+  T rhs[20];
+  {  // pole block, and its coupling to the cart-pole rows through the pole
+    T j[12][3], d[12][3];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) lam_row1<SMEM>(gp + i * SW1, j[i], d[i], rhs[i], S.invd[i]);
+#pragma unroll
+    for (int i = 4; i < 12; ++i) {
+      if (fr) lam_row1<SMEM>(fgp + (i - 4) * SW1, j[i], d[i], rhs[i], S.invd[i]);
+      else { j[i][0] = j[i][1] = j[i][2] = 0; d[i][0] = d[i][1] = d[i][2] = 0; rhs[i] = 0; S.invd[i] = 0; }
+    }
+#pragma unroll
+    for (int i = 0; i < 12; ++i)
+#pragma unroll
+      for (int k = 0; k <= i; ++k) S.Ap[tri(i, k)] = dot3(j[i], j[k]) + imp * dot3(d[i], d[k]);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      SRow2<T> r;
+      load_row<SMEM>(cp + i * SW2, r);
+      const T jb[3] = {r.a[3], r.b[0], r.b[1]}, n[3] = {r.b[2], r.b[3], r.c[0]};
+#pragma unroll
+      for (int k = 0; k < 12; ++k) S.Acp[i * 12 + k] = dot3(jb, j[k]) - imp * dot3(n, d[k]);  // the normal pushes the pole with -n
+    }
+  }
+  {  // the cart's side
+    T ja[4][3], jb[4][3], n[4][3], jg[4][3], dg[4][3];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      SRow2<T> r;
+      load_row<SMEM>(cp + i * SW2, r);
+      ja[i][0] = r.a[0]; ja[i][1] = r.a[1]; ja[i][2] = r.a[2];
+      jb[i][0] = r.a[3]; jb[i][1] = r.b[0]; jb[i][2] = r.b[1];
+      n[i][0] = r.b[2]; n[i][1] = r.b[3]; n[i][2] = r.c[0];
+      rhs[12 + i] = r.c[1]; S.invd[12 + i] = r.c[2];
+      lam_row1<SMEM>(gc + i * SW1, jg[i], dg[i], rhs[16 + i], S.invd[16 + i]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+#pragma unroll
+      for (int k = 0; k <= i; ++k) {
+        S.Ac[tri(i, k)] = (dot3(ja[i], ja[k]) + dot3(jb[i], jb[k])) + (imc + imp) * dot3(n[i], n[k]);
+        S.Ag[tri(i, k)] = dot3(jg[i], jg[k]) + imc * dot3(dg[i], dg[k]);
+      }
+#pragma unroll
+      for (int k = 0; k < 4; ++k) S.Acg[i * 4 + k] = dot3(ja[i], jg[k]) + imc * dot3(n[i], dg[k]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 20; ++i)  // warm start; friction starts at 0
+    S.lam[i] = i < 4 ? apn[SLOT_GP + i] : (i < 12 ? T(0.0) : (i < 16 ? apn[SLOT_CP + (i - 12)] : apn[SLOT_GC + (i - 16)]));
+#pragma unroll
+  for (int i = 0; i < 12; ++i) {
+    T acc = rhs[i];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) acc -= S.Ap[tri(i, k)] * S.lam[k];
+#pragma unroll
+    for (int m = 0; m < 4; ++m) acc -= S.Acp[m * 12 + i] * S.lam[12 + m];
+    S.res[i] = acc;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    T acc = rhs[12 + i], ag = rhs[16 + i];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      acc -= S.Ac[tri(i, k)] * S.lam[12 + k];
+      acc -= S.Acg[i * 4 + k] * S.lam[16 + k];
+      acc -= S.Acp[i * 12 + k] * S.lam[k];
+      ag -= S.Ag[tri(i, k)] * S.lam[16 + k];
+      ag -= S.Acg[k * 4 + i] * S.lam[12 + k];
+    }
+    S.res[12 + i] = acc;
+    S.res[16 + i] = ag;
+  }
+}
+template <typename T> BCP_HD T gen_normal(LamGen<T>& S, int i, T cfm, T& delta) {
+  const T D = fast_rcp(S.invd[i]);
+  const T u = S.res[i] - S.lam[i] * cfm;
+  delta = u * S.invd[i];
+  return clamp_normal(S.lam[i], delta, u, D);
+}
+// one iteration, solve_iteration's order: ground-pole, cart-pole, ground-cart normals, then the ground-pole friction pairs;
+// all four slots of every block (slots an env does not use are zero rows)
+template <bool FRICTION, typename T> BCP_HD T lam_round_gen(const Params<T>& P, bool fr, LamGen<T>& S) {
+  T lsr = 0;
+  const T cfm = P.cfm_normal, cfm_f = P.cfm_friction;
+#define BCP_GACC(r_) { const T r__ = (r_); const T r2__ = r__ * r__; lsr = lsr > r2__ ? lsr : r2__; }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {  // ground-pole normals
+    T dl;
+    BCP_GACC(gen_normal(S, i, cfm, dl));
+#pragma unroll
+    for (int k = 0; k < 12; ++k) S.res[k] -= S.Ap[tri(k, i)] * dl;
+#pragma unroll
+    for (int m = 0; m < 4; ++m) S.res[12 + m] -= S.Acp[m * 12 + i] * dl;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {  // cart-pole
+    T dl;
+    BCP_GACC(gen_normal(S, 12 + i, cfm, dl));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { S.res[12 + k] -= S.Ac[tri(k, i)] * dl; S.res[16 + k] -= S.Acg[i * 4 + k] * dl; }
+#pragma unroll
+    for (int k = 0; k < 12; ++k) S.res[k] -= S.Acp[i * 12 + k] * dl;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {  // ground-cart
+    T dl;
+    BCP_GACC(gen_normal(S, 16 + i, cfm, dl));
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { S.res[16 + k] -= S.Ag[tri(k, i)] * dl; S.res[12 + k] -= S.Acg[k * 4 + i] * dl; }
+  }
+  if (FRICTION && fr) {
+    const T mu = P.mu[BCP_PAIR_GROUND_POLE];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) {
+      const int a = 4 + 2 * c, b = 5 + 2 * c;
+      const T DA = fast_rcp(S.invd[a]), DB = fast_rcp(S.invd[b]);
+      const T uB = S.res[b] - S.lam[b] * cfm_f, uA = S.res[a] - S.lam[a] * cfm_f;
+      T dB = uB * S.invd[b], dA = uA * S.invd[a];
+      BCP_GACC(cone_clip(S.lam[a], S.lam[b], dA, dB, uA, uB, DA, DB, mu * S.lam[c]));
+#pragma unroll
+      for (int k = 0; k < 12; ++k) { S.res[k] -= S.Ap[tri(k, a)] * dA; S.res[k] -= S.Ap[tri(k, b)] * dB; }
+#pragma unroll
+      for (int m = 0; m < 4; ++m) { S.res[12 + m] -= S.Acp[m * 12 + a] * dA; S.res[12 + m] -= S.Acp[m * 12 + b] * dB; }
+    }
+  }
+#undef BCP_GACC
+  return lsr;
+}
+template <bool SMEM, bool FRICTION, typename T>
+BCP_HD void lam_finish_gen(const Params<T>& P, const T* colp, const SolveLayout& L, const LamGen<T>& S, SolveRegs<T>& R) {
+  const T* const gp = colp + L.base[BCP_PAIR_GROUND_POLE];
+  const T* const cp = colp + L.base[BCP_PAIR_CART_POLE];
+  const T* const gc = colp + L.base[BCP_PAIR_GROUND_CART];
+  const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+  const T* const fgp = colp + (fr ? L.fbase[BCP_PAIR_GROUND_POLE] : 0);
+  for (int i = 0; i < 3; ++i) { R.cart.wt[i] = 0; R.cart.dv[i] = 0; R.pole.wt[i] = 0; R.pole.dv[i] = 0; }
+  for (int s = 0; s < N_SLOTS; ++s) R.apn[s] = 0;
+#pragma unroll
+  for (int i = 0; i < 12; ++i) {
+    if (i >= 4 && !fr) break;
+    T j[3], d[3], rhs, invd;
+    lam_row1<SMEM>(i < 4 ? gp + i * SW1 : fgp + (i - 4) * SW1, j, d, rhs, invd);
+    const T l = S.lam[i], lm = P.pole.inv_mass * l;
+    R.pole.wt[0] += j[0] * l; R.pole.wt[1] += j[1] * l; R.pole.wt[2] += j[2] * l;
+    R.pole.dv[0] += d[0] * lm; R.pole.dv[1] += d[1] * lm; R.pole.dv[2] += d[2] * lm;
+    if (i < 4) R.apn[SLOT_GP + i] = l;
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    SRow2<T> r;
+    load_row<SMEM>(cp + i * SW2, r);
+    const T l = S.lam[12 + i], la = P.cart.inv_mass * l, lb = P.pole.inv_mass * l;
+    R.cart.wt[0] += r.a[0] * l; R.cart.wt[1] += r.a[1] * l; R.cart.wt[2] += r.a[2] * l;
+    R.pole.wt[0] += r.a[3] * l; R.pole.wt[1] += r.b[0] * l; R.pole.wt[2] += r.b[1] * l;
+    R.cart.dv[0] += r.b[2] * la; R.cart.dv[1] += r.b[3] * la; R.cart.dv[2] += r.c[0] * la;
+    R.pole.dv[0] -= r.b[2] * lb; R.pole.dv[1] -= r.b[3] * lb; R.pole.dv[2] -= r.c[0] * lb;
+    R.apn[SLOT_CP + i] = l;
+    T j[3], d[3], rhs, invd;
+    lam_row1<SMEM>(gc + i * SW1, j, d, rhs, invd);
+    const T g = S.lam[16 + i], lm = P.cart.inv_mass * g;
+    R.cart.wt[0] += j[0] * g; R.cart.wt[1] += j[1] * g; R.cart.wt[2] += j[2] * g;
+    R.cart.dv[0] += d[0] * lm; R.cart.dv[1] += d[1] * lm; R.cart.dv[2] += d[2] * lm;
+    R.apn[SLOT_GC + i] = g;
+  }
+}
+
 }  // namespace bcp

@@ -232,6 +232,16 @@ BCP_HD void substep_split_reference(const Params<T>& P, Env<T>& st, T* rec, Subs
     }
     if (lmode == LAM_STACK) lam_finish_stack<false>(P, rec + REC_ROWS, L, Sy, R);
     else lam_finish_split<false, FRICTION>(P, rec + REC_ROWS, L, Sy, R);
+  } else if (lam_config_ok(P) && !getenv("BCP_NO_LAMBDA") && !getenv("BCP_NO_LAMGEN")) {  // k_solve_gen_once's iteration
+    LamGen<T> Sy;
+    const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+    lam_build_gen<false, FRICTION>(P, rec + REC_ROWS, L, R.apn, Sy);
+    for (int k = 0; k < P.solver_iterations; ++k) {
+      const T lsr = lam_round_gen<FRICTION>(P, fr, Sy);
+      it = k + 1;
+      if (lsr <= P.residual_thr || k >= P.solver_iterations - 1) break;
+    }
+    lam_finish_gen<false, FRICTION>(P, rec + REC_ROWS, L, Sy, R);
   } else {
     for (int k = 0; k < P.solver_iterations; ++k) {
       const T lsr = solve_iteration<T, FRICTION>(P, rec + REC_ROWS, L, cnt, R);
@@ -875,6 +885,68 @@ __global__ void __launch_bounds__(kBlock, 2) k_solve_lam_once(const __grid_const
       solve_end(rec, S, it, R);
     }
     __syncwarp();  // the columns are reused by the warp's next chunk
+  }
+}
+// The generic queue (pole touching cart AND ground: a few dozen envs per launch) in impulse space, one env per lane, one
+// chunk of the queue per warp, to convergence (bcp_lambda.cuh, LamGen).  These solves mostly run all 50 iterations; row by
+// row (k_solve) they were the longest dependent chain of the solve phase and the next k_prep waited for them: capping them
+// at 30 iterations - wrong on purpose, as a measurement - shortened env.step by 7 %.
+template <typename T, bool FRICTION>
+__global__ void __launch_bounds__(kBlock, 1) k_solve_gen_once(const __grid_constant__ Params<T> P, T* __restrict__ recs, int rec_words,
+                                                              const int2* __restrict__ queue, int* __restrict__ qc, int col_stride) {
+  const unsigned FULL = 0xffffffffu;
+  T* const smem = reinterpret_cast<T*>(bcp_smem);
+  const int lane = threadIdx.x & 31, warp_base = threadIdx.x - lane;
+  T* const col = smem + (size_t)threadIdx.x * col_stride;
+  const SolveLayout L = solve_layout(P);
+  const int N = P.num_envs;
+  PoolFeed<T> feed;  // its piece table and queue geometry; nothing is fetched through it
+  feed.init(L, lane, rec_words, qc, N);
+  SolveScale<T> S;
+  {
+    SolveRegs<T> R0;
+    solve_consts(P, R0, S);
+  }
+  const bool fr = FRICTION && L.fbase[BCP_PAIR_GROUND_POLE] >= 0;
+  const T res_thr = P.residual_thr;
+  const int max_it = P.solver_iterations;
+  const int warps = gridDim.x * (blockDim.x >> 5);
+  for (int w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); w * 32 < feed.total; w += warps) {
+    const int idx = w * 32 + lane;
+    const bool have = idx < feed.total;
+    int env = 0, meta = 0;
+    if (have) {
+      const int2 q = queue[idx < feed.n_long ? idx : N - 1 - (idx - feed.n_long)];
+      env = q.x;
+      meta = q.y;
+    }
+    feed.stage(__ballot_sync(FULL, have), lane, env, meta, recs, rec_words, smem, warp_base, col_stride);
+    cp_async_wait_all();
+    __syncwarp();
+    LamGen<T> Sy;
+    int it = 0;
+    if (have) {
+      int cnt[3];
+      SolveRegs<T> R;
+      solve_load(col, S, cnt, R);  // counts and warm-start impulses
+      lam_build_gen<true, FRICTION>(P, col + REC_ROWS, L, R.apn, Sy);
+    }
+    bool open = have;
+    while (__any_sync(FULL, open)) {
+      if (open) {
+        const T lsr = lam_round_gen<FRICTION>(P, fr, Sy);
+        it++;
+        if (lsr <= res_thr || it >= max_it) open = false;
+      }
+    }
+    if (have) {
+      SolveRegs<T> R;
+      R.cart.invM = P.cart.inv_mass;
+      R.pole.invM = P.pole.inv_mass;
+      lam_finish_gen<true, FRICTION>(P, col + REC_ROWS, L, Sy, R);
+      solve_end(recs + (size_t)env * rec_words, S, it, R);
+    }
+    __syncwarp();
   }
 }
 // The solves k_solve_lam handed off, one per lane, 32 consecutive continuation slots per warp (all

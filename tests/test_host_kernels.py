@@ -110,3 +110,58 @@ def test_pipelined_machine_equals_oracle_with_synchronous_resets():
             waited[fresh] = 0
             n_fresh += int(fresh.sum())
     assert n_fresh >= n
+
+
+def test_generic_regime_in_impulse_space_against_oracle():
+    """States in which the pole touches the cart AND the ground (the regime neither STACK nor SPLIT covers, LamGen in
+    bcp_lambda.cuh, k_solve_gen_once on the GPU), collected from an oracle rollout of the bench workload: one substep of the
+    split pipeline's host composition in fp64 vs the oracle - same contacts, same iteration counts, state within 1e-10 -
+    and the fp32 instantiation against the row-space sweep it replaces (BCP_NO_LAMGEN)."""
+    import os
+    n = 1024
+    cfg = _cfg(n, initial_force=200.0, action_force=100.0)
+    ora = Oracle(cfg, dtype="fp64")
+    ora.reset()
+    rng = np.random.default_rng(7)
+    found = []
+    for t in range(120):
+        ora.step(rng.uniform(-1, 1, size=(n, 2)).astype(np.float32))
+        probe = Oracle(cfg, dtype="fp64")
+        probe.state[:] = ora.state
+        probe.state[:, C.S_DONE] = 0
+        before = probe.state.copy()
+        info = probe.substep(with_info=True)
+        gen = (info[:, 3 + 1] > 0) & (info[:, 3 + 2] > 0)  # contacts of cart-pole and ground-pole
+        found.append(before[gen])
+        if sum(len(f) for f in found) >= 64:
+            break
+    st = np.concatenate(found)
+    assert len(st) >= 16, "the rollout met too few states of the generic regime"
+    m = len(st)
+    cfg_m = _cfg(m, initial_force=200.0, action_force=100.0)
+    ora_m, spl = Oracle(cfg_m, dtype="fp64"), HostKernels(cfg_m, "fp64", fast=2)
+    ora_m.state[:] = st
+    spl.state[:] = st
+    i_o, i_s = ora_m.substep(with_info=True), spl.substep(with_info=True)
+    assert (i_o[:, 4] > 0).all() and (i_o[:, 5] > 0).all()
+    assert np.array_equal(i_o, i_s)
+    assert np.abs(ora_m.state - spl.state)[:, :C.S_MANI_CNT].max() <= 1e-10
+    assert (i_o[:, 0] >= 50).any(), "no solve of the sample ran all the iterations"
+    # fp32: impulse space vs the row-space sweep from the same states
+    cfg32 = _cfg(m, dtype="fp32", initial_force=200.0, action_force=100.0)
+    st32 = st.astype(np.float32).astype(np.float64)
+    a = HostKernels(cfg32, "fp32", fast=2)
+    a.state[:] = st32
+    ia = a.substep(with_info=True)
+    os.environ["BCP_NO_LAMGEN"] = "1"
+    try:
+        b = HostKernels(cfg32, "fp32", fast=2)
+        b.state[:] = st32
+        ib = b.substep(with_info=True)
+    finally:
+        del os.environ["BCP_NO_LAMGEN"]
+    d = np.abs(a.state - b.state)
+    pose = np.concatenate([d[:, 0:7], d[:, 13:20]], axis=1).max(axis=1)  # positions and quaternions (north_star's 1e-4)
+    same_it = ia[:, 0] == ib[:, 0]
+    assert np.median(pose) <= 1e-6 and (pose[same_it] <= 1e-4).all(), (np.median(pose), pose.max())
+    assert same_it.mean() >= 0.8
