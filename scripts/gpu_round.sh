@@ -24,6 +24,7 @@ python scripts/prof_split.py > $O/${TAG}_prof_plain.log 2>&1 && {
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_solve_lam -s 8 -c 1 -f -o $O/${TAG}_k_solve_lam python scripts/prof_split.py > $O/${TAG}_ncu_solve.log 2>&1
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_solve_tail -s 8 -c 1 -f -o $O/${TAG}_k_solve_tail python scripts/prof_split.py > $O/${TAG}_ncu_tail.log 2>&1
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_prep -s 13 -c 1 -f -o $O/${TAG}_k_prep python scripts/prof_split.py > $O/${TAG}_ncu_prep.log 2>&1
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_solve_gen_once -s 8 -c 1 -f -o $O/${TAG}_k_solve_gen_once python scripts/prof_split.py > $O/${TAG}_ncu_gen.log 2>&1
 }
 unset BCP_GRAPH BCP_SPLIT
 for f in $O/${TAG}_bench_*.json; do python - "$f" <<'PY'
