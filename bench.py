@@ -656,7 +656,7 @@ def main():
     ap.add_argument("--span", type=int, default=200, help="env.steps the timed steps are spread over (>= --steps: every span/steps-th step is timed)")
     ap.add_argument("--no-configs3", action="store_true", help="N >= 2: skip the configs[3] run (1 M envs sharded, deciles)")
     ap.add_argument("--configs3-envs", type=int, default=1048576)
-    ap.add_argument("--e2e-parts", type=int, default=2, help="the e2e host loop drives the batch as this many parts, multi-buffered")
+    ap.add_argument("--e2e-parts", type=int, default=4, help="the e2e host loop drives the batch as this many parts, multi-buffered")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-secondary", action="store_true", help="skip the labelled workloads reported beside the headline (upstream-style friction; fast reset)")
     ap.add_argument("--no-carry-over-reset", action="store_true", help="reset() clears the pending force and the contact caches (deviation from pybullet)")
