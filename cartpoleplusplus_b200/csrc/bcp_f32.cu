@@ -136,7 +136,10 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   for (int k = 0; k <= RS; ++k) {
     const int s_fin = k - 1, s_set = (k < RS) ? k : -1;
     int* qc = b.qc + (size_t)(k < RS ? k : 0) * 3 * Q_WORDS;
-    k_prep<float, FRICTION><<<prep_grid, prep_block, prep_smem, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set, use_lam);
+    if (s_set >= 0)
+      k_prep<float, FRICTION><<<prep_grid, prep_block, prep_smem, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, s_set, use_lam);
+    else  // the closing kernel: the lean instance (no frame, four blocks per SM)
+      k_prep<float, FRICTION, false><<<(N + kBlock - 1) / kBlock, kBlock, 0, s>>>(P, f, id, b.recs, rec_words, reinterpret_cast<int2*>(b.queue), qc, io, st, vo, s_fin, -1, use_lam);
     if (launches) ++*launches;
     if (b.after_prep) b.after_prep(b.hook_ctx, k, s);
     mark();

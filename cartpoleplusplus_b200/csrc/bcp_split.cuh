@@ -339,11 +339,15 @@ constexpr int kPrepGround = 16;
 constexpr int kPrepFrame = (int)(sizeof(SetupFrame<float>) / sizeof(float)) | 1;
 inline size_t prep_smem_bytes(int block) { return sizeof(float) * ((size_t)kPrepGround + (size_t)block * kPrepFrame); }
 __device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-template <typename T, bool FRICTION>
-__global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
+// SETUP = false: the instance for the kernel that closes a call (s_set < 0).  It has no narrowphase, no manifold work and
+// no rows to write, so it needs neither the shared-memory frame nor 240 registers: compiled without the set-up branch it
+// runs at four blocks per SM instead of two (the slots of resident warps are what bounds the step).
+template <typename T, bool FRICTION, bool SETUP = true>
+__global__ void __launch_bounds__(kBlock, SETUP ? BCP_PREP_MINB : 4) k_prep(const __grid_constant__ Params<T> P, T* __restrict__ f, int* __restrict__ id,
                                                  T* __restrict__ recs, int rec_words, int2* __restrict__ queue,
                                                  int* __restrict__ qc_set, SplitIO io, Stats stats, VisitOrder vo, int s_fin,
-                                                 int s_set, int use_lam) {
+                                                 int s_set_arg, int use_lam) {
+  const int s_set = SETUP ? s_set_arg : -1;
   const int N = P.num_envs;
   const int e_visit = visit(vo, blockIdx.x * blockDim.x + threadIdx.x, N);
   const bool valid = e_visit >= 0;
@@ -416,7 +420,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
   bool q_on = false, q_gen = false, q_long = false;  // the env's queue entry (written at the end of the kernel)
   unsigned ml = 0, ms = 0, mg = 0;
   int bl = 0, bs = 0, bg = 0;
-  if (s_set >= 0) {
+  if (SETUP && s_set >= 0) {
     const bool on = valid && substep_on(mode, st);
     if (!on) last_iters = 0;
     SetupCtx<T> C;
@@ -506,7 +510,7 @@ __global__ void __launch_bounds__(kBlock, BCP_PREP_MINB) k_prep(const __grid_con
     store_env_core<T>(f, id, e, st);
     id[(size_t)e * NI + I_MODE] = mode;
   }
-  if (s_set >= 0) {  // the queue entry, at the slots the atomics above handed out
+  if (SETUP && s_set >= 0) {  // the queue entry, at the slots the atomics above handed out
     const int lane = threadIdx.x & 31;
     bl = __shfl_sync(0xffffffffu, bl, 0);
     bs = __shfl_sync(0xffffffffu, bs, 0);
