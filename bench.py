@@ -403,7 +403,7 @@ def run_ours(args):
         halves.append(he)
     host_actions = [[torch.empty((nh[i], 2), dtype=torch.float32).pin_memory().uniform_(-1, 1) for _ in range(2)] for i in range(parts)]
     Ke = max(3, K)
-    for t in range(2):
+    for t in range(2 * max(1, (max(W, 3) + 1) // 2)):  # W untimed steps (an even number: both buffer / graph parities) through the same API
         for i in range(parts):
             halves[i].step_host(host_actions[i][t % 2])
     if world > 1:
