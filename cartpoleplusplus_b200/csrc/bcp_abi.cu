@@ -665,6 +665,32 @@ int bcp_rollout_random(bcp_env* h, int32_t n_steps, uint32_t action_set_mask, in
   bcp::Params<double> p64 = h->p64;
   bcp::Params<float> p32 = h->p32;
   p64.auto_reset = p32.auto_reset = BCP_AUTO_RESET_PIPELINED;  // a rollout resets its envs in place
+  const char* rv = getenv("BCP_ROLLOUT_SPLIT");  // read per call: tests compare the two paths in one process
+  const int roll_split = rv ? atoi(rv) : 1;
+  if (!h->f64() && h->use_split && roll_split && !h->profiling) {
+    // the same n_steps calls of the pipelined machine as k_rollout runs in one launch, through the split pipeline (three times
+    // the env-steps/s at these batch sizes): per call, the agent's actions (k_draw_actions), then the pipeline's kernels
+    const uint32_t mask = action_set_mask & 0x1fu;
+    int rc = 0;
+    for (bcp_env::Cohort& co : h->cohorts) {
+      co.b.roll_max_episodes = max_episodes;
+      co.b.rollout = 1;
+      co.P.auto_reset = BCP_AUTO_RESET_PIPELINED;
+    }
+    for (int t = 0; t < n_steps && rc == 0; ++t) {
+      if (bcp::launch_draw_actions(p32, h->idata, h->act_buf, mask, s) != cudaSuccess) { rc = -1; break; }
+      int n = 1;
+      rc = enqueue_split(h, h->act_buf, obs_out, nullptr, nullptr, nullptr, s, &n);
+      h->launches += n;
+    }
+    for (bcp_env::Cohort& co : h->cohorts) {
+      co.b.roll_max_episodes = 0;
+      co.b.rollout = 0;
+      co.P.auto_reset = h->p32.auto_reset;
+    }
+    if (rc) return fail("bcp_rollout_random: split pipeline launch", cudaGetLastError());
+    return 0;
+  }
   if (h->f64()) CK(bcp::Launch<double>::rollout(p64, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
   else CK(bcp::Launch<float>::rollout(p32, h->fdata, h->idata, n_steps, action_set_mask & 0x1fu, max_episodes, obs_out, h->stats(), s));
   h->launches++;

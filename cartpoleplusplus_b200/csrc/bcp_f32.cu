@@ -185,9 +185,15 @@ cudaError_t launch_step_split(const Params<float>& P, float* f, int* id, SplitBu
                               float* reward, uint8_t* done, uint8_t* reason, StatsPtrs sp, cudaStream_t s, int* launches,
                               std::vector<cudaEvent_t>* prof, size_t obs_env_stride, size_t obs_rep_stride) {
   const Stats st{sp.hist, sp.header, sp.reward_sum};
-  const SplitIO io{actions, obs, reward, done, reason, obs_env_stride ? obs_env_stride : (size_t)14 * P.R, obs_rep_stride ? obs_rep_stride : (size_t)14};
+  const SplitIO io{actions, obs, reward, done, reason, obs_env_stride ? obs_env_stride : (size_t)14 * P.R, obs_rep_stride ? obs_rep_stride : (size_t)14,
+                   b.roll_max_episodes, b.rollout};
   if (P.any_friction) return step_split_impl<true>(P, f, id, b, io, st, s, launches, prof);
   return step_split_impl<false>(P, f, id, b, io, st, s, launches, prof);
+}
+
+cudaError_t launch_draw_actions(const Params<float>& P, const int* id, void* actions, uint32_t mask, cudaStream_t s) {
+  k_draw_actions<float><<<(P.num_envs + 255) / 256, 256, 0, s>>>(P, id, actions, mask);
+  return cudaGetLastError();
 }
 
 cudaError_t launch_compact(const uint8_t* flag, int n, int* list, int* count, cudaStream_t s) {

@@ -52,7 +52,10 @@ struct SplitBuffers {
   int trace_stride;  // envs per substep block of `trace` (the handle's env count: a cohort's buffers are views)
   int lam;           // impulse-space solve phase on the main queue: decided once per handle (-1: from this view's size)
   int side_ready;    // the lazily created side stream / kernel attributes exist (or are not needed): the call can be captured
+  int roll_max_episodes, rollout;  // set by bcp_rollout_random around its calls (SplitIO::max_episodes / rollout)
 };
+// the random agent's actions of the next call into `actions` (bcp_rollout_random through the split pipeline)
+cudaError_t launch_draw_actions(const Params<float>& P, const int* id, void* actions, uint32_t mask, cudaStream_t s);
 size_t split_cont_words(const Params<float>& P);
 bool split_uses_lambda(const Params<float>& P);  // impulse-space solve phase for this configuration / batch size?
 size_t split_bins_words(const Params<float>& P);

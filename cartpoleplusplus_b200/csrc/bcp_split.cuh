@@ -274,6 +274,10 @@ struct SplitIO {
   // layout of `obs`: floats between two envs and between two repeats of an env.  (14 R, 14): the (B, R, 2, 7) block of
   // bcp_step; (14, 14 B): repeat-major slabs [R][B][2][7], what bcp_step_host copies to the host slab by slab
   size_t env_stride, rep_stride;
+  // bcp_rollout_random through this pipeline: > 0 parks an env that is done with `episode` >= max_episodes (it has delivered
+  // its share of the protocol's episodes), and the closing kernel also accumulates the rollout's counters (substeps, resets,
+  // reward sum - step() returns the rewards to its caller instead)
+  int max_episodes, rollout;
 };
 
 // Visiting order of the envs.  The kernel that closes a call files every env under its contact
@@ -392,7 +396,8 @@ __global__ void __launch_bounds__(kBlock, SETUP ? BCP_PREP_MINB : 4) k_prep(cons
   }
   if (s_fin < 0) {
     const bool idle_done = valid && st.done && st.reset_left == 0;
-    mode = call_begin(P, st, valid, false);
+    const bool parked = io.max_episodes > 0 && idle_done && st.episode >= io.max_episodes;
+    mode = call_begin(P, st, valid && !parked, false);
     if (P.settled && idle_done && mode != MODE_IDLE) {  // a reset began on the cached post-settle state: its manifold blocks too
 #pragma unroll
       for (int m = 0; m < 3; ++m)
@@ -490,6 +495,15 @@ __global__ void __launch_bounds__(kBlock, SETUP ? BCP_PREP_MINB : 4) k_prep(cons
     if (stats.header) {
       const unsigned w = __popc(__ballot_sync(0xffffffffu, live));
       if ((threadIdx.x & 31) == 0 && w) atomicAdd(&stats.header[1], (unsigned long long)w);
+      if (io.rollout) {  // k_rollout's other counters: substeps of every env that took part in the call, finished resets, reward
+        const unsigned on_n = __popc(__ballot_sync(0xffffffffu, valid && mode != MODE_IDLE));
+        const unsigned fr_n = __popc(__ballot_sync(0xffffffffu, valid && rs == BCP_REASON_FRESH));
+        if ((threadIdx.x & 31) == 0) {
+          if (on_n) atomicAdd(&stats.header[2], (unsigned long long)on_n * (unsigned long long)(P.R * P.S));
+          if (fr_n) atomicAdd(&stats.header[3], (unsigned long long)fr_n);
+          if (w && stats.reward_sum) atomicAdd(stats.reward_sum, (double)w);
+        }
+      }
     }
     if (vo.next_cnt) {  // file the env under the contact regime its next call will run in
       int key = (st.mani[BCP_PAIR_GROUND_POLE].count > 0 ? 4 : 0) | (st.mani[BCP_PAIR_CART_POLE].count > 0 ? 2 : 0) |
@@ -522,6 +536,22 @@ __global__ void __launch_bounds__(kBlock, SETUP ? BCP_PREP_MINB : 4) k_prep(cons
     else if (q_gen) queue[N + N - 1 - (bg + __popc(mg & lt))] = entry;
     else if (q_on) queue[N - 1 - (bs + __popc(ms & lt))] = entry;
   }
+}
+
+// bcp_rollout_random through the split pipeline: the random agent's action of every env for the call that follows, the same
+// draw as k_rollout's (Philox keyed by global env id, episode and step: draw_action, bcp_episode.cuh)
+template <typename T>
+__global__ void k_draw_actions(const __grid_constant__ Params<T> P, const int* __restrict__ id, void* __restrict__ actions, uint32_t mask) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= P.num_envs) return;
+  Env<T> st;
+  st.episode = id[(size_t)e * NI + I_EPISODE];
+  st.steps = id[(size_t)e * NI + I_STEPS];
+  int a = 0;
+  float ax = 0.f, ay = 0.f;
+  draw_action(P, P.env_id_offset + e, st, mask, a, ax, ay);
+  if (P.discrete) reinterpret_cast<int32_t*>(actions)[e] = a;
+  else reinterpret_cast<float2*>(actions)[e] = make_float2(ax, ay);
 }
 
 // persistent pooled solve: every lane keeps pulling envs until the queue is dry.
