@@ -203,7 +203,10 @@ int bcp_step(bcp_env* env, const void* actions, float* obs_out, float* reward_ou
  *                     (the protocol's --num-eval split over the envs; makes the
  *                     histogram independent of n_calls and of the sharding);
  *                     0: no limit
- *   obs_out may be NULL; else the envs' latest observation                  */
+ *   obs_out may be NULL; else the envs' latest observation
+ * fp32 handles of >= 4 096 envs run the n_calls rounds through the split pipeline
+ * (the action draw as a kernel of its own before each round's kernels); smaller
+ * and fp64 handles in one launch.  Same machine and action stream either way.  */
 int bcp_rollout_random(bcp_env* env, int32_t n_calls, uint32_t action_set_mask,
                        int32_t max_episodes, float* obs_out, void* stream);
 
