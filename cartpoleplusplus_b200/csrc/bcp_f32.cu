@@ -122,6 +122,7 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
   }
   const int solve_grid = min(sms * per_sm, (N + L.block - 1) / L.block);
   const int gen_grid = side ? min(solve_grid, 16) : solve_grid;
+  const int gen_once_grid = min((N + L.block - 1) / L.block, 4 * sms);
   static int prep_block = 0;
   if (!prep_block) {
     const char* pb = getenv("BCP_PREP_BLOCK");
@@ -149,7 +150,10 @@ static cudaError_t step_split_impl(const Params<float>& P, float* f, int* id, Sp
           cudaEventRecord(b.ev_prep, s);
           cudaStreamWaitEvent(b.side, b.ev_prep, 0);
           if (lam_gen)  // impulse space for these too: half the latency per iteration of solves that mostly run all 50
-            k_solve_gen_once<float, FRICTION><<<gen_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride);
+            // one warp per 32 queued envs; blocks past the queue's end leave at once.  Normally a block or two have work; a batch
+            // whose envs were all reset together sends a wave of them through this regime at the same time (poles falling off
+            // the carts: tens of thousands of 50-iteration solves in the same calls), which 16 blocks took 20 ms to work off.
+            k_solve_gen_once<float, FRICTION><<<gen_once_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride);
           else
             k_solve<float, FRICTION><<<gen_grid, L.block, L.smem, b.side>>>(P, b.recs, rec_words, reinterpret_cast<const int2*>(b.queue) + N, qc + Q_WORDS, col_stride, fetch_min);
           cudaEventRecord(b.ev_gen, b.side);
