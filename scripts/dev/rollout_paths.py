@@ -1,5 +1,5 @@
 """configs[3]-style rollout (one episode per env, in-kernel random agent) through the split pipeline and through the
-one-launch k_rollout: device time and env-steps/s.  Usage: python scripts/dev/dbg_roll.py [envs]"""
+one-launch k_rollout: device time and env-steps/s.  Usage: python scripts/dev/rollout_paths.py [envs]"""
 import os, sys, time
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
